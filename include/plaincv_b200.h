@@ -1,0 +1,98 @@
+/* plaincv_b200.h — C ABI of libplaincv_b200.so: the sm_100a kernels behind the training-step hot path of
+ * GeorgTirp/plainCV's models/LM causal Transformer (fwd + bwd of train_lm.py:compute_grads).
+ *
+ * The reference has no FFI of its own (it is pure JAX/Flax; every op below is "whatever XLA emits"), so each
+ * entry point cites the reference *operation* it replaces (file:line under the reference checkout).  All
+ * functions:
+ *   - take raw device pointers, sizes and a cudaStream_t (as void*); they never allocate and never synchronise;
+ *   - return 0 on success, a positive cudaError_t, or one of the negative PCV_ERR_* codes below;
+ *   - are re-entrant (the only global state is a mutex-guarded cache of TMA descriptors).
+ * Activations are bf16 row-major [tokens, features]; master parameters and gradients are fp32.
+ */
+#ifndef PLAINCV_B200_H_
+#define PLAINCV_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCV_OK 0
+#define PCV_ERR_ARG (-1)    /* bad shape / null pointer / unsupported combination */
+#define PCV_ERR_ALIGN (-2)  /* pointer or leading dimension violates the 16-byte rule of TMA / vector access */
+#define PCV_ERR_TMAP (-3)   /* cuTensorMapEncodeTiled failed */
+#define PCV_ERR_DRIVER (-4) /* driver entry point unavailable */
+
+/* GEMM epilogues */
+#define PCV_EPI_BF16 0       /* C bf16  = alpha * acc              */
+#define PCV_EPI_F32_ATOMIC 1 /* C fp32 += alpha * acc (red.add; split-K allowed) */
+#define PCV_EPI_F32 2        /* C fp32  = alpha * acc              */
+
+int pcv_version(void);
+/* Number of kernels this library has launched in the calling process since load (bench.py's gpu_launches). */
+long long pcv_launch_count(void);
+
+/* C[M,N] (=|+=) alpha * sum_k A(m,k) B(n,k); bf16 operands, fp32 accumulate (tcgen05 / TMEM).
+ * a_mn_major = 0: A stored [M][lda] (k contiguous); 1: A stored [K][lda] (m contiguous).  Same for B with N.
+ * Replaces flax.linen.Dense on the hot path — models/LM/transformer.py:110-134 (fc_gate/fc_up/fc2),
+ * :194-201 (w_qkv), :246-253 (w_out), :398-405 (lm_head) — and their autodiff transposes (train_lm.py:267). */
+int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                  int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream);
+
+/* fp32 master -> bf16 compute copy, zero-filling the padded tail columns: dst[rows][dst_ld] <- src[rows][src_ld][:cols].
+ * Replaces flax's per-call promote_dtype of `kernel`/`embedding` (transformer.py: every nn.Dense / nn.Embed). */
+int pcv_cast_pad_bf16(const float* src, void* dst, int rows, int cols, int src_ld, int dst_ld, void* stream);
+
+/* x[m,:] = bf16(E[ids[m],:])                         — nn.Embed, models/LM/transformer.py:361-369 */
+int pcv_embed_fwd(const int32_t* ids, const void* table_bf16, void* x, int M, int d, void* stream);
+/* dE[ids[m],:] += dx[m,:] (fp32 atomics)              — transpose of the gather above */
+int pcv_embed_bwd(const int32_t* ids, const void* dx, float* dE, int M, int d, int ldE, void* stream);
+
+/* Residual add fused with RMSNorm — Block: x = x + f(norm(x)), models/LM/transformer.py:293,334 with
+ * nn.RMSNorm :41-47 (fp32 statistics, eps inside the rsqrt, bf16 output).
+ *   res_out = res_in + delta   (delta may be NULL: plain norm of res_in)
+ *   y       = bf16( fp32(res_out) * rsqrt(mean(res_out^2) + eps) * scale )
+ *   rstd[m] saved for backward. */
+int pcv_rmsnorm_residual_fwd(const void* res_in, const void* delta, const float* scale, void* res_out, void* y,
+                             float* rstd, int M, int d, float eps, void* stream);
+/* Backward of the above. dres_out: gradient arriving at res_out from later consumers (may be NULL);
+ * dy: gradient of y.  Writes dres_in (= d delta) and accumulates dscale (fp32 atomics). */
+int pcv_rmsnorm_residual_bwd(const void* dy, const void* dres_out, const void* res_out, const float* scale,
+                             const float* rstd, void* dres_in, float* dscale, int M, int d, void* stream);
+
+/* h = silu(g) * u with [g | u] the two halves of gu[M][2*hid] — GLU, models/LM/transformer.py:126 */
+int pcv_swiglu_fwd(const void* gu, void* h, int M, int hid, void* stream);
+int pcv_swiglu_bwd(const void* gu, const void* dh, void* dgu, int M, int hid, void* stream);
+
+/* cos/sin table [T][hd/2] (float2) — precompute_freqs_cis, models/LM/embedding.py:8-26 */
+int pcv_rope_table(float* cos_sin, int T, int head_dim, float theta, void* stream);
+
+/* Flash-style attention over qkv[B*T][3*d] (columns [q|k|v], each head-major [N][hd], hd = 64) with interleaved-pair
+ * RoPE applied to q and k on load (models/LM/embedding.py:28-67) and softmax(q k^T / sqrt(hd) + mask) v
+ * (jax.nn.dot_product_attention at models/LM/transformer.py:233-240).  Mask: causal, intersected with document
+ * blocks when doc_start != NULL (doc_start[b*T + t] = first position of the document containing t; the
+ * block-diagonal mask of data/datasets/data_prep_utils.py:14-43, never materialised).
+ * out[B*T][d] bf16; lse[B][N][T] fp32 saved for backward. */
+int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, void* out, float* lse, int B, int T,
+                 int n_heads, void* stream);
+/* dqkv[B*T][3*d] from dout; delta[B][N][T] is fp32 scratch (rowsum(dout*out)). */
+int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out, const void* dout,
+                 const float* lse, float* delta, void* dqkv, int B, int T, int n_heads, void* stream);
+
+/* Softmax cross-entropy over bf16 logits[M][ldl] (first V columns valid) with integer labels — _loss_and_acc,
+ * train_lm.py:181-186 (fp32 logsumexp - logit[label], mean over all M tokens; acc = first-max argmax == label).
+ * Writes per-row loss/correct into row_loss/row_correct and, if dlogits != NULL, overwrites
+ * dlogits[M][ldl] = (softmax - onehot) * grad_scale (pad columns zero); dlogits may alias logits. */
+int pcv_softmax_ce(const void* logits, const int32_t* labels, void* dlogits, float* row_loss, float* row_correct,
+                   int M, int V, int ldl, float grad_scale, void* stream);
+/* out[0] = sum(row_loss)/M, out[1] = sum(row_correct)/M  (deterministic single-block reduction) */
+int pcv_mean2(const float* row_loss, const float* row_correct, float* out, int M, void* stream);
+
+/* out[i] += in[i] (bf16), helper for gradient joins of the residual stream */
+int pcv_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLAINCV_B200_H_ */

@@ -1,0 +1,401 @@
+// gemm.cu — persistent, warp-specialised tcgen05/TMEM GEMM for sm_100a, fed by TMA.
+//
+// Replaces every `flax.linen.Dense` contraction on the reference's training hot path
+// (reference: models/LM/transformer.py:110-134 GLU, :194-201 w_qkv, :246-253 w_out, :398-405 lm_head) and the
+// dgrad / wgrad contractions XLA derives from them (train_lm.py:267 value_and_grad).
+//
+//   C[M,N] (=|+=)  sum_k A(m,k) * B(n,k)       bf16 operands, fp32 accumulation in tensor memory
+//
+// Operand storage (either operand, independently):
+//   K-major  : stored [rows = M or N][K]  (contraction contiguous)        -> TMA box {64 k, rows}
+//   MN-major : stored [K][cols = M or N]  (output dimension contiguous)   -> TMA boxes {64 mn, 64 k}
+// With the reference's (in,out) `kernel` layout this gives, without any transposed weight copy:
+//   forward  Y = X W        : A = X  K-major, B = W  MN-major
+//   dgrad    dX = dY W^T    : A = dY K-major, B = W  K-major
+//   wgrad    dW += X^T dY   : A = X  MN-major, B = dY MN-major, fp32 red.add epilogue (split-K)
+//
+// Structure (one CTA per SM, 256 threads):
+//   warp 0   : TMA producer (one elected lane)      smem ring of kStages {A,B} tiles, mbarrier full/empty
+//   warp 1   : MMA issuer (one elected lane)        tcgen05.mma 128 x BN x 16, accumulators double-buffered in TMEM
+//   warp 2   : TMEM allocator
+//   warps 4-7: epilogue                             tcgen05.ld -> registers -> global (bf16 / fp32 / fp32 red.add)
+#include "sm100.cuh"
+#include "pcv_internal.h"
+
+#include <mutex>
+#include <unordered_map>
+
+namespace pcv {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;
+constexpr int kGemmThreads = 256;
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kABytes = kBM * kBK * 2;  // 16 KB
+  static constexpr int kBBytes = BN * kBK * 2;   // 32 / 16 KB
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // +1024 for manual alignment
+  static constexpr uint32_t kTmemCols = 2 * BN;                              // 512 or 256
+};
+
+struct GemmParams {
+  void* C;
+  int M, N, K;
+  int ldc;
+  int m_tiles, n_tiles, splits, kb_per_split, kb_total;
+  float alpha;
+};
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t smem_a = smem_base;
+  const uint32_t smem_b = smem_base + Cfg::kStages * Cfg::kABytes;
+  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+  auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + s); };
+  auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + 2 + s); };
+  const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * Cfg::kStages + 4);
+  volatile uint32_t* tmem_ptr_generic =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tmem_full_bar(s), 1);
+      mbar_init(tmem_empty_bar(s), 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<Cfg::kTmemCols>(tmem_ptr_smem);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_generic;
+
+  const int total_work = p.m_tiles * p.n_tiles * p.splits;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int n_blk = w % p.n_tiles;
+        const int m_blk = (w / p.n_tiles) % p.m_tiles;
+        const int split = w / (p.n_tiles * p.m_tiles);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const int m0 = m_blk * kBM, n0 = n_blk * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_expect_tx(full_bar(stage), Cfg::kStageBytes);
+          const uint32_t sa = smem_a + stage * Cfg::kABytes;
+          const uint32_t sb = smem_b + stage * Cfg::kBBytes;
+          const int k0 = kb * kBK;
+          if constexpr (!A_MN) {
+            tma_load_2d(sa, &tma_a, full_bar(stage), k0, m0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < kBM / 64; ++i) tma_load_2d(sa + i * (64 * kBK * 2), &tma_a, full_bar(stage), m0 + 64 * i, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(sb, &tma_b, full_bar(stage), k0, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i) tma_load_2d(sb + i * (64 * kBK * 2), &tma_b, full_bar(stage), n0 + 64 * i, k0);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, A_MN, B_MN);
+      // per-UMMA_K(16) advance inside a stage: K-major 32 B along the swizzled row; MN-major 16 rows of 128 B
+      constexpr uint32_t a_kstep = A_MN ? 16 * 128 : 32;
+      constexpr uint32_t b_kstep = B_MN ? 16 * 128 : 32;
+      constexpr uint32_t a_lbo = A_MN ? 64 * kBK * 2 : 16, b_lbo = B_MN ? 64 * kBK * 2 : 16;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
+        const int split = w / (p.n_tiles * p.m_tiles);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(tmem_empty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_a + stage * Cfg::kABytes;
+          const uint32_t sb = smem_b + stage * Cfg::kBBytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+            const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+            umma_bf16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(empty_bar(stage));  // smem slot reusable once these MMAs have read it
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit(tmem_full_bar(acc));  // accumulator complete -> epilogue
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int ew = warp & 3;  // TMEM lane quarter this warp may access
+    int it = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
+      const int n_blk = w % p.n_tiles;
+      const int m_blk = (w / p.n_tiles) % p.m_tiles;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tmem_full_bar(acc), acc_phase);
+      tc_fence_after();
+      const int row = m_blk * kBM + ew * 32 + lane;
+      const int n0 = n_blk * BN;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        if (row < p.M && col0 < p.N) {
+          if constexpr (EPI == PCV_EPI_BF16) {
+            __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              if (col0 + v * 8 + 8 <= p.N) {
+                uint4 o;
+                o.x = pack_bf16x2(__uint_as_float(r[v * 8 + 0]) * p.alpha, __uint_as_float(r[v * 8 + 1]) * p.alpha);
+                o.y = pack_bf16x2(__uint_as_float(r[v * 8 + 2]) * p.alpha, __uint_as_float(r[v * 8 + 3]) * p.alpha);
+                o.z = pack_bf16x2(__uint_as_float(r[v * 8 + 4]) * p.alpha, __uint_as_float(r[v * 8 + 5]) * p.alpha);
+                o.w = pack_bf16x2(__uint_as_float(r[v * 8 + 6]) * p.alpha, __uint_as_float(r[v * 8 + 7]) * p.alpha);
+                *reinterpret_cast<uint4*>(crow + v * 8) = o;
+              }
+            }
+          } else {
+            float* crow = reinterpret_cast<float*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
+#pragma unroll
+            for (int v = 0; v < 8; ++v) {
+              if (col0 + v * 4 + 4 <= p.N) {
+                const float x0 = __uint_as_float(r[v * 4 + 0]) * p.alpha, x1 = __uint_as_float(r[v * 4 + 1]) * p.alpha;
+                const float x2 = __uint_as_float(r[v * 4 + 2]) * p.alpha, x3 = __uint_as_float(r[v * 4 + 3]) * p.alpha;
+                if constexpr (EPI == PCV_EPI_F32_ATOMIC) {
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(crow + v * 4), "f"(x0), "f"(x1),
+                               "f"(x2), "f"(x3)
+                               : "memory");
+                } else {
+                  *reinterpret_cast<float4*>(crow + v * 4) = make_float4(x0, x1, x2, x3);
+                }
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty_bar(acc));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 row-major [rows][cols] (ld elements between rows), 128B-swizzled box {64, box_rows}.
+int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) return PCV_ERR_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 2) % 16) return PCV_ERR_ALIGN;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PCV_OK : PCV_ERR_TMAP;
+}
+
+namespace {
+struct TmapKey {
+  const void* ptr;
+  uint64_t rows, cols, ld;
+  uint32_t box_rows;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.ptr);
+    h = h * 1000003u ^ k.rows;
+    h = h * 1000003u ^ k.cols;
+    h = h * 1000003u ^ k.ld;
+    h = h * 1000003u ^ k.box_rows;
+    return h;
+  }
+};
+std::mutex g_tmap_mu;
+std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
+}  // namespace
+
+// Descriptors depend only on (pointer, shape, box): cache them, the training step re-uses the same buffers.
+int get_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  TmapKey key{ptr, rows, cols, ld, box_rows};
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mu);
+    auto it = g_tmap_cache.find(key);
+    if (it != g_tmap_cache.end()) {
+      *out = it->second;
+      return PCV_OK;
+    }
+  }
+  int rc = make_tmap_2d_bf16(out, ptr, rows, cols, ld, box_rows);
+  if (rc != PCV_OK) return rc;
+  std::lock_guard<std::mutex> g(g_tmap_mu);
+  if (g_tmap_cache.size() > 65536) g_tmap_cache.clear();
+  g_tmap_cache.emplace(key, *out);
+  return PCV_OK;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_set = true;
+  }
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(ta, tb, p);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                        cudaStream_t st) {
+  switch (epi) {
+    case PCV_EPI_BF16: return launch_gemm<BN, A_MN, B_MN, PCV_EPI_BF16>(ta, tb, p, grid, st);
+    case PCV_EPI_F32_ATOMIC: return launch_gemm<BN, A_MN, B_MN, PCV_EPI_F32_ATOMIC>(ta, tb, p, grid, st);
+    case PCV_EPI_F32: return launch_gemm<BN, A_MN, B_MN, PCV_EPI_F32>(ta, tb, p, grid, st);
+  }
+  return PCV_ERR_ARG;
+}
+
+template <int BN>
+static int dispatch_major(int a_mn, int b_mn, int epi, const CUtensorMap& ta, const CUtensorMap& tb,
+                          const GemmParams& p, int grid, cudaStream_t st) {
+  if (!a_mn && !b_mn) return dispatch_epi<BN, false, false>(epi, ta, tb, p, grid, st);
+  if (!a_mn && b_mn) return dispatch_epi<BN, false, true>(epi, ta, tb, p, grid, st);
+  if (a_mn && !b_mn) return dispatch_epi<BN, true, false>(epi, ta, tb, p, grid, st);
+  return dispatch_epi<BN, true, true>(epi, ta, tb, p, grid, st);
+}
+
+}  // namespace pcv
+
+extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                             int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream) {
+  using namespace pcv;
+  if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return PCV_ERR_ARG;
+  if (splits < 1) splits = 1;
+  if (epilogue != PCV_EPI_F32_ATOMIC && splits != 1) return PCV_ERR_ARG;
+  const int vec = (epilogue == PCV_EPI_BF16) ? 8 : 4;
+  if (N % vec || ldc % vec || (reinterpret_cast<uintptr_t>(C) & 15)) return PCV_ERR_ALIGN;
+
+  // tile-N choice: 256 unless the problem cannot fill the machine with 128x256 tiles
+  const int m_tiles = (M + kBM - 1) / kBM;
+  int BN = 256;
+  {
+    const long t256 = static_cast<long>(m_tiles) * ((N + 255) / 256) * splits;
+    if (N <= 128 || t256 < 2L * num_sms()) BN = 128;
+  }
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = get_tmap_2d_bf16(&ta, A, M, K, lda, kBM);
+  else rc = get_tmap_2d_bf16(&ta, A, K, M, lda, 64);
+  if (rc) return rc;
+  if (!b_mn_major) rc = get_tmap_2d_bf16(&tb, B, N, K, ldb, BN);
+  else rc = get_tmap_2d_bf16(&tb, B, K, N, ldb, 64);
+  if (rc) return rc;
+
+  GemmParams p;
+  p.C = C;
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+  p.m_tiles = m_tiles;
+  p.n_tiles = (N + BN - 1) / BN;
+  p.kb_total = (K + kBK - 1) / kBK;
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.alpha = alpha;
+  const long total = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
+  const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (BN == 256) return dispatch_major<256>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
+  return dispatch_major<128>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
+}
