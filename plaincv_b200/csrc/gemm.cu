@@ -396,6 +396,7 @@ extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   const long total = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  count_launch();
   if (BN == 256) return dispatch_major<256>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
   return dispatch_major<128>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
 }

@@ -1,0 +1,182 @@
+// loss.cu — softmax cross-entropy over bf16 logits with integer labels, producing the per-row loss, the first-max
+// argmax accuracy and (in the same pass over the row, held in shared memory) d(logits) for the LM-head backward.
+// Restates _loss_and_acc (train_lm.py:181-186): fp32 logsumexp(logits) - logits[label], mean over all tokens.
+// HBM-bound: one read of the bf16 row + one write of the bf16 gradient row.
+#include "sm100.cuh"
+#include "pcv_internal.h"
+#include <float.h>
+
+namespace pcv {
+
+constexpr int kCeThreads = 512;
+
+struct MaxIdx {
+  float m;
+  int i;
+};
+__device__ __forceinline__ MaxIdx better(MaxIdx a, MaxIdx b) {  // larger value wins; ties -> smaller index
+  return (b.m > a.m || (b.m == a.m && b.i < a.i)) ? b : a;
+}
+
+// One block per row.  If kCache, the row is staged in shared memory so HBM sees it exactly once.
+template <bool kCache>
+__global__ void __launch_bounds__(kCeThreads)
+softmax_ce_kernel(const __nv_bfloat16* __restrict__ logits, const int32_t* __restrict__ labels,
+                  __nv_bfloat16* __restrict__ dlogits, float* __restrict__ row_loss, float* __restrict__ row_correct,
+                  int V, int ldl, float grad_scale) {
+  extern __shared__ uint4 row_cache[];  // ldl/8 vectors when kCache
+  __shared__ float s_m[kCeThreads / 32], s_s[kCeThreads / 32];
+  __shared__ int s_i[kCeThreads / 32];
+  __shared__ float s_bcast[2];
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const __nv_bfloat16* lrow = logits + static_cast<long>(row) * ldl;
+  const int nvec = ldl / 8;
+  const int label = labels[row];
+
+  // pass 1: online max / sum-exp, argmax (first max)
+  float m = -FLT_MAX, s = 0.f;
+  MaxIdx best{-FLT_MAX, 0x7fffffff};
+  for (int v = tid; v < nvec; v += kCeThreads) {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(lrow) + v);
+    if (kCache) row_cache[v] = raw;
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 t = unpack_bf16x2(w[j]);
+      f[2 * j] = t.x;
+      f[2 * j + 1] = t.y;
+    }
+    float vm = -FLT_MAX;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = v * 8 + j;
+      if (c < V) {
+        vm = fmaxf(vm, f[j]);
+        if (f[j] > best.m) { best.m = f[j]; best.i = c; }
+      }
+    }
+    if (vm > m) { s *= __expf(m - vm); m = vm; }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (v * 8 + j < V) s += __expf(f[j] - m);
+  }
+  // warp reduce
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, m, o), os = __shfl_xor_sync(0xffffffffu, s, o);
+    const float nm = fmaxf(m, om);
+    s = s * __expf(m - nm) + os * __expf(om - nm);
+    m = nm;
+    MaxIdx ob{__shfl_xor_sync(0xffffffffu, best.m, o), __shfl_xor_sync(0xffffffffu, best.i, o)};
+    best = better(best, ob);
+  }
+  if (lane == 0) { s_m[warp] = m; s_s[warp] = s; s_i[warp] = best.i; }
+  __syncthreads();
+  if (warp == 0) {
+    float bm = (lane < kCeThreads / 32) ? s_m[lane] : -FLT_MAX;
+    float bs = (lane < kCeThreads / 32) ? s_s[lane] : 0.f;
+    // the per-warp argmax carries the warp max as its value
+    MaxIdx bb{bm, (lane < kCeThreads / 32) ? s_i[lane] : 0x7fffffff};
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, bm, o), os = __shfl_xor_sync(0xffffffffu, bs, o);
+      const float nm = fmaxf(bm, om);
+      bs = bs * __expf(bm - nm) + os * __expf(om - nm);
+      bm = nm;
+      MaxIdx ob{__shfl_xor_sync(0xffffffffu, bb.m, o), __shfl_xor_sync(0xffffffffu, bb.i, o)};
+      bb = better(bb, ob);
+    }
+    if (lane == 0) {
+      const float lse = bm + logf(bs);
+      const float picked = __bfloat162float(lrow[label]);
+      row_loss[row] = lse - picked;
+      row_correct[row] = (bb.i == label) ? 1.f : 0.f;
+      s_bcast[0] = lse;
+    }
+  }
+  if (dlogits == nullptr) return;
+  __syncthreads();
+  const float lse = s_bcast[0];
+  __nv_bfloat16* drow = dlogits + static_cast<long>(row) * ldl;
+  for (int v = tid; v < nvec; v += kCeThreads) {
+    const uint4 raw = kCache ? row_cache[v] : *(reinterpret_cast<const uint4*>(lrow) + v);
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 t = unpack_bf16x2(w[j]);
+      g[2 * j] = t.x;
+      g[2 * j + 1] = t.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = v * 8 + j;
+      float p = (c < V) ? __expf(g[j] - lse) : 0.f;
+      if (c == label) p -= 1.f;
+      g[j] = p * grad_scale;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(g[0], g[1]); o.y = pack_bf16x2(g[2], g[3]);
+    o.z = pack_bf16x2(g[4], g[5]); o.w = pack_bf16x2(g[6], g[7]);
+    *(reinterpret_cast<uint4*>(drow) + v) = o;
+  }
+}
+
+__global__ void __launch_bounds__(1024) mean2_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                      float* __restrict__ out, int M) {
+  __shared__ double sa[32], sb[32];
+  double xa = 0, xb = 0;
+  for (int i = threadIdx.x; i < M; i += blockDim.x) { xa += a[i]; xb += b[i]; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    xa += __shfl_xor_sync(0xffffffffu, xa, o);
+    xb += __shfl_xor_sync(0xffffffffu, xb, o);
+  }
+  if ((threadIdx.x & 31) == 0) { sa[threadIdx.x >> 5] = xa; sb[threadIdx.x >> 5] = xb; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ta = 0, tb = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) { ta += sa[w]; tb += sb[w]; }
+    out[0] = static_cast<float>(ta / M);
+    out[1] = static_cast<float>(tb / M);
+  }
+}
+
+}  // namespace pcv
+
+using namespace pcv;
+
+extern "C" int pcv_softmax_ce(const void* logits, const int32_t* labels, void* dlogits, float* row_loss,
+                              float* row_correct, int M, int V, int ldl, float grad_scale, void* stream) {
+  if (!logits || !labels || !row_loss || !row_correct || M <= 0 || V <= 0 || V > ldl) return PCV_ERR_ARG;
+  if (ldl % 8 || (reinterpret_cast<uintptr_t>(logits) & 15) || (dlogits && (reinterpret_cast<uintptr_t>(dlogits) & 15)))
+    return PCV_ERR_ALIGN;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t row_bytes = static_cast<size_t>(ldl) * 2;
+  if (row_bytes <= 200 * 1024) {
+    auto kern = softmax_ce_kernel<true>;
+    static bool attr = false;
+    if (!attr) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      attr = true;
+    }
+    kern<<<M, kCeThreads, row_bytes, st>>>(static_cast<const __nv_bfloat16*>(logits), labels,
+                                           static_cast<__nv_bfloat16*>(dlogits), row_loss, row_correct, V, ldl, grad_scale);
+  } else {
+    softmax_ce_kernel<false><<<M, kCeThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(logits), labels,
+                                                       static_cast<__nv_bfloat16*>(dlogits), row_loss, row_correct, V,
+                                                       ldl, grad_scale);
+  }
+  count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_mean2(const float* row_loss, const float* row_correct, float* out, int M, void* stream) {
+  if (!row_loss || !row_correct || !out || M <= 0) return PCV_ERR_ARG;
+  mean2_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(row_loss, row_correct, out, M);
+  count_launch();
+  return cuda_rc();
+}
