@@ -65,20 +65,19 @@ int pcv_rmsnorm_residual_bwd(const void* dy, const void* dres_out, const void* r
 int pcv_swiglu_fwd(const void* gu, void* h, int M, int hid, void* stream);
 int pcv_swiglu_bwd(const void* gu, const void* dh, void* dgu, int M, int hid, void* stream);
 
-/* cos/sin table [T][hd/2] (float2) — precompute_freqs_cis, models/LM/embedding.py:8-26 */
-int pcv_rope_table(float* cos_sin, int T, int head_dim, float theta, void* stream);
-
 /* Flash-style attention over qkv[B*T][3*d] (columns [q|k|v], each head-major [N][hd], hd = 64) with interleaved-pair
- * RoPE applied to q and k on load (models/LM/embedding.py:28-67) and softmax(q k^T / sqrt(hd) + mask) v
+ * RoPE applied to q and k on load (models/LM/embedding.py:28-67; cos_sin = fp32 [T][32][2] = (cos, sin) of
+ * precompute_freqs_cis, embedding.py:8-26, built once by the host) and softmax(q k^T / sqrt(hd) + mask) v
  * (jax.nn.dot_product_attention at models/LM/transformer.py:233-240).  Mask: causal, intersected with document
  * blocks when doc_start != NULL (doc_start[b*T + t] = first position of the document containing t; the
  * block-diagonal mask of data/datasets/data_prep_utils.py:14-43, never materialised).
  * out[B*T][d] bf16; lse[B][N][T] fp32 saved for backward. */
 int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, void* out, float* lse, int B, int T,
                  int n_heads, void* stream);
-/* dqkv[B*T][3*d] from dout; delta[B][N][T] is fp32 scratch (rowsum(dout*out)). */
+/* dqkv[B*T][3*d] from dout.  Scratch supplied by the caller: delta[B][N][T] fp32 (rowsum(dout*out)) and
+ * dq_acc[B*T][d] fp32 (zeroed here; dQ partials of the key tiles are red.add-ed into it, then un-rotated). */
 int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out, const void* dout,
-                 const float* lse, float* delta, void* dqkv, int B, int T, int n_heads, void* stream);
+                 const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int n_heads, void* stream);
 
 /* Softmax cross-entropy over bf16 logits[M][ldl] (first V columns valid) with integer labels — _loss_and_acc,
  * train_lm.py:181-186 (fp32 logsumexp - logit[label], mean over all M tokens; acc = first-max argmax == label).

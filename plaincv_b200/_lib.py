@@ -1,0 +1,80 @@
+"""ctypes binding of libplaincv_b200.so (the C ABI declared in include/plaincv_b200.h).
+
+There is deliberately no fallback: if the shared library is missing or a symbol cannot be resolved the import of
+any compute path raises, and a kernel returning a non-zero status raises `KernelError`.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_longlong, c_void_p
+from typing import Optional
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libplaincv_b200.so")
+
+PCV_EPI_BF16 = 0
+PCV_EPI_F32_ATOMIC = 1
+PCV_EPI_F32 = 2
+
+_ERR = {
+    -1: "PCV_ERR_ARG (bad shape / null pointer / unsupported combination)",
+    -2: "PCV_ERR_ALIGN (pointer or leading dimension violates the 16-byte rule)",
+    -3: "PCV_ERR_TMAP (cuTensorMapEncodeTiled failed)",
+    -4: "PCV_ERR_DRIVER (driver entry point unavailable)",
+}
+
+# name -> (restype, argtypes); mirrors include/plaincv_b200.h one to one
+SIGNATURES = {
+    "pcv_version": (c_int, []),
+    "pcv_launch_count": (c_longlong, []),
+    "pcv_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                              c_int, c_int, c_float, c_void_p]),
+    "pcv_cast_pad_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "pcv_embed_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "pcv_embed_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "pcv_rmsnorm_residual_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                         c_float, c_void_p]),
+    "pcv_rmsnorm_residual_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                         c_int, c_void_p]),
+    "pcv_swiglu_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "pcv_swiglu_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "pcv_attn_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "pcv_attn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                             c_int, c_int, c_int, c_void_p]),
+    "pcv_softmax_ce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
+                               c_void_p]),
+    "pcv_mean2": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "pcv_add_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_longlong, c_void_p]),
+}
+
+
+class KernelError(RuntimeError):
+    pass
+
+
+_lib: Optional[ctypes.CDLL] = None
+
+
+def load() -> ctypes.CDLL:
+    """Load the shared library (once) and type every entry point.  Raises if it is absent: there is no CPU path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C plaincv_b200/csrc`). plaincv_b200 has no CPU or PyTorch fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = _ERR.get(rc, f"cudaError_t {rc}" if rc > 0 else f"status {rc}")
+        raise KernelError(f"{what} failed: {msg}")

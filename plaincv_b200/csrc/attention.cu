@@ -1,0 +1,803 @@
+// attention.cu — flash-style causal / document-masked attention forward and backward on tcgen05 + TMEM for sm_100a,
+// head_dim = 64, with the interleaved-pair RoPE of the reference fused into the Q/K tile load.
+//
+// Replaces, on the reference's hot path (all XLA-generated there, O(T^2) memory):
+//   apply_rotary_emb_complex_like      models/LM/embedding.py:28-67   (call: models/LM/transformer.py:212)
+//   jax.nn.dot_product_attention       models/LM/transformer.py:233-240  (fp32 logits/softmax, bf16 P before P.V)
+//   the bool [B,T,T] block-diagonal mask of train_lm.py:107-131 / data_prep_utils.py:14-43 — consumed here as
+//   doc_start[b*T+t] (first position of t's document); the [T,T] mask is never built.
+// and their autodiff transposes (train_lm.py:267).
+//
+// Layout: qkv[B*T][3d] bf16, columns [q | k | v], each third head-major [N][64].  out[B*T][d] bf16.
+// lse[B][N][T] fp32 (natural log).  Tiles are 128 rows x 64 columns = 128 x 128 B, 128B-swizzled in shared memory:
+// K-major operand for Q.K^T, and the *same bytes* serve as the MN-major operand of P.V / dS^T.Q / P^T.dO.
+//
+// Forward CTA (416 threads) = one (batch, head, 256-query block):
+//   warps 0-3 / 4-7 : softmax warpgroup 0 / 1, one thread per query row of its 128-row tile; S read from TMEM in two
+//                     passes (row max, then exp2 + bf16 P into shared memory); the running output is kept in registers
+//                     and folded with the per-tile P.V read back from TMEM one tile late (so it overlaps the MMAs)
+//   warps 8-11      : loader — global -> RoPE in registers -> swizzled shared memory for Q and K; TMA for V
+//   warp 12         : tcgen05.mma issuer (one lane): S_w = Q_w.K_j^T, O_w,j = P_w.V_j, ping-ponged between the two
+//                     warpgroups so one group's MMAs run under the other's exponentials
+// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 {[256,320),[320,384)} O1 {[384,448),[448,512)}.
+//
+// Backward CTA (416 threads) = one (batch, head, 128-key tile), looping over the query tiles that can see it:
+//   S = Q_i.K^T, dP = dO_i.V^T  ->  P = exp2(S*c - lse), dS = P*(dP - delta)*scale (256 threads, half a row each)
+//   dV += P^T.dO_i, dK += dS^T.Q_i (accumulated in TMEM over the loop), dQ_i = dS.K (read back, red.add into fp32 dq)
+// TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448).
+#include "sm100.cuh"
+#include "pcv_internal.h"
+#include <math.h>
+
+namespace pcv {
+
+constexpr int kAttnThreads = 416;
+constexpr int kTileBytes = 128 * 128;  // 128 rows x 64 bf16
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kSoftmaxScale = 0.125f;  // 1/sqrt(64)
+
+__device__ __forceinline__ float ex2f(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_global_nc_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Rotate the 4 interleaved pairs held in one 16-byte chunk.  cs0 = (cos0, sin0, cos1, sin1), cs1 = (cos2, sin2, cos3, sin3).
+// sign = +1: forward rotation (embedding.py:58-59); sign = -1: its transpose (gradient).
+__device__ __forceinline__ uint4 rope_chunk(uint4 raw, float4 cs0, float4 cs1, float sign) {
+  const float2 p0 = unpack_bf16x2(raw.x), p1 = unpack_bf16x2(raw.y), p2 = unpack_bf16x2(raw.z), p3 = unpack_bf16x2(raw.w);
+  uint4 o;
+  o.x = pack_bf16x2(p0.x * cs0.x - sign * p0.y * cs0.y, p0.y * cs0.x + sign * p0.x * cs0.y);
+  o.y = pack_bf16x2(p1.x * cs0.z - sign * p1.y * cs0.w, p1.y * cs0.z + sign * p1.x * cs0.w);
+  o.z = pack_bf16x2(p2.x * cs1.x - sign * p2.y * cs1.y, p2.y * cs1.x + sign * p2.x * cs1.y);
+  o.w = pack_bf16x2(p3.x * cs1.z - sign * p3.y * cs1.w, p3.y * cs1.z + sign * p3.x * cs1.w);
+  return o;
+}
+
+// 128 threads (ltid 0..127) load rows [t0, t0+128) x 64 columns of one sequence, apply RoPE at position t, and store
+// the tile 128B-swizzled.  8 lanes cover one 128-byte row (coalesced), 16 rows per step.  Rows >= T are zero-filled.
+__device__ __forceinline__ void load_rope_tile(uint32_t smem_tile, const __nv_bfloat16* __restrict__ gcol, int ld,
+                                               long grow0, int t0, int T, const float* __restrict__ cos_sin, int ltid) {
+  const int c = ltid & 7, rsub = ltid >> 3;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int r = it * 16 + rsub;
+    const int t = t0 + r;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (t < T) {
+      const uint4 raw = ld_global_nc_v4(gcol + (grow0 + r) * ld + c * 8);
+      const float4* cs = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(t) * 32 + c * 4) * 2);
+      v = rope_chunk(raw, __ldg(cs), __ldg(cs + 1), 1.f);
+    }
+    st_shared_v4(smem_tile + r * 128 + ((c ^ (r & 7)) << 4), v);
+  }
+}
+
+// ================================================================================================ forward
+struct AttnFwdSmem {
+  static constexpr int kQ = 0;                          // 2 tiles
+  static constexpr int kK = kQ + 2 * kTileBytes;        // 3 slots
+  static constexpr int kV = kK + 3 * kTileBytes;        // 3 slots
+  static constexpr int kP = kV + 3 * kTileBytes;        // 2 x (128 x 128 bf16)
+  static constexpr int kBar = kP + 2 * 2 * kTileBytes;  // barriers
+  static constexpr int kBytes = kBar + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16* __restrict__ qkv,
+                const float* __restrict__ cos_sin, const int32_t* __restrict__ doc_start,
+                __nv_bfloat16* __restrict__ out, float* __restrict__ lse, int T, int NH) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sQ = sbase + AttnFwdSmem::kQ, sK = sbase + AttnFwdSmem::kK, sV = sbase + AttnFwdSmem::kV,
+                 sP = sbase + AttnFwdSmem::kP, sBar = sbase + AttnFwdSmem::kBar;
+  // barrier map (8 bytes each)
+  const uint32_t bQ = sBar;                                     // q_ready            (128)
+  auto bKready = [&](int s) { return sBar + 8u * (1 + s); };    // [3]                (128)
+  auto bVfull = [&](int s) { return sBar + 8u * (4 + s); };     // [3]                (tx)
+  auto bKVempty = [&](int s) { return sBar + 8u * (7 + s); };   // [3]                (1, commit)
+  auto bSfull = [&](int w) { return sBar + 8u * (10 + w); };    // [2]                (1, commit)
+  auto bPfull = [&](int w) { return sBar + 8u * (12 + w); };    // [2]                (128)
+  auto bOfull = [&](int w, int b) { return sBar + 8u * (14 + 2 * w + b); };  // [2][2] (1, commit)
+  const uint32_t tmem_ptr_smem = sBar + 8u * 18;
+  volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_qblk = gridDim.x;
+  const int qblk = n_qblk - 1 - blockIdx.x;  // heaviest (latest) query blocks first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int d = NH * 64, ld = 3 * d;
+  const int q0 = qblk * 256;
+  const long seq_row0 = static_cast<long>(b) * T;
+
+  // per-warpgroup key-tile ranges [jmin_w, jmax_w]
+  int jmin[2], jmax[2];
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+    const int r0 = q0 + 128 * w;
+    if (r0 < T) {
+      jmax[w] = r0 / 128;
+      jmin[w] = doc_start ? (doc_start[seq_row0 + r0] / 128) : 0;
+    } else {
+      jmax[w] = -1;
+      jmin[w] = 0;
+    }
+  }
+  const int jlo = jmin[0];
+  const int jhi = jmax[1] >= 0 ? jmax[1] : jmax[0];
+  auto active = [&](int w, int j) { return j >= jmin[w] && j <= jmax[w]; };
+
+  if (warp == 12 && lane == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    mbar_init(bQ, 128);
+    for (int s = 0; s < 3; ++s) {
+      mbar_init(bKready(s), 128);
+      mbar_init(bVfull(s), 1);
+      mbar_init(bKVempty(s), 1);
+    }
+    for (int w = 0; w < 2; ++w) {
+      mbar_init(bSfull(w), 1);
+      mbar_init(bPfull(w), 128);
+      mbar_init(bOfull(w, 0), 1);
+      mbar_init(bOfull(w, 1), 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 11) tmem_alloc<512>(tmem_ptr_smem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_generic;
+
+  if (warp >= 8 && warp < 12) {
+    // ============================== loader warps ==============================
+    const int ltid = tid - 256;
+    const __nv_bfloat16* qcol = qkv + h * 64;
+    const __nv_bfloat16* kcol = qkv + d + h * 64;
+#pragma unroll
+    for (int w = 0; w < 2; ++w)
+      if (jmax[w] >= 0) load_rope_tile(sQ + w * kTileBytes, qcol, ld, seq_row0 + q0 + 128 * w, q0 + 128 * w, T, cos_sin, ltid);
+    fence_proxy_async_smem();
+    mbar_arrive(bQ);
+    int idx = 0;
+    for (int j = jlo; j <= jhi; ++j, ++idx) {
+      const int slot = idx % 3;
+      const uint32_t use_par = (idx / 3) & 1;
+      mbar_wait(bKVempty(slot), use_par ^ 1u);
+      if (ltid == 0) {
+        mbar_expect_tx(bVfull(slot), kTileBytes);
+        tma_load_2d(sV + slot * kTileBytes, &tm_qkv, bVfull(slot), 2 * d + h * 64, static_cast<int>(seq_row0) + j * 128);
+      }
+      load_rope_tile(sK + slot * kTileBytes, kcol, ld, seq_row0 + j * 128, j * 128, T, cos_sin, ltid);
+      fence_proxy_async_smem();
+      mbar_arrive(bKready(slot));
+    }
+  } else if (warp == 12) {
+    // ============================== MMA issuer ==============================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);
+      auto issue_S = [&](int w, int slot) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = umma_smem_desc(sQ + w * kTileBytes + k * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sK + slot * kTileBytes + k * 32, 16, 1024);
+          umma_bf16_ss(tmem_base + w * 128, da, db, idesc_s, k > 0 ? 1u : 0u);
+        }
+        tc_commit(bSfull(w));
+      };
+      auto issue_PV = [&](int w, int slot, int obuf) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          // A = P_w (K-major, two 64-key atoms 16 KB apart); B = V (MN-major: one 128-byte row per key)
+          const uint64_t da = umma_smem_desc(sP + w * 2 * kTileBytes + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sV + slot * kTileBytes + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tmem_base + 256 + w * 128 + obuf * 64, da, db, idesc_pv, k > 0 ? 1u : 0u);
+        }
+        tc_commit(bOfull(w, obuf));
+      };
+      mbar_wait(bQ, 0);
+      tc_fence_after();
+      // prologue: first S of each warpgroup active at jlo
+      mbar_wait(bKready(0), 0);
+      tc_fence_after();
+#pragma unroll
+      for (int w = 0; w < 2; ++w)
+        if (active(w, jlo)) issue_S(w, 0);
+      int idx = 0;
+      for (int j = jlo; j <= jhi; ++j, ++idx) {
+        const int slot = idx % 3;
+        const uint32_t use_par = (idx / 3) & 1;
+        const int last_w = active(1, j) ? 1 : 0;
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+          if (active(w, j)) {
+            const int i = j - jmin[w];
+            mbar_wait(bPfull(w), i & 1);
+            mbar_wait(bVfull(slot), use_par);
+            tc_fence_after();
+            issue_PV(w, slot, i & 1);
+          }
+          if (w == last_w) tc_commit(bKVempty(slot));
+          if (j + 1 <= jhi && active(w, j + 1)) {
+            const int slot1 = (idx + 1) % 3;
+            mbar_wait(bKready(slot1), ((idx + 1) / 3) & 1);
+            tc_fence_after();
+            issue_S(w, slot1);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ============================== softmax warpgroups ==============================
+    const int w = warp >> 2;
+    const int r = tid & 127;
+    if (jmax[w] >= 0) {
+      const int t = q0 + 128 * w + r;
+      const int ds_t = doc_start ? doc_start[seq_row0 + min(t, T - 1)] : 0;
+      const int ds_hi = doc_start ? doc_start[seq_row0 + min(q0 + 128 * w + 127, T - 1)] : 0;
+      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+      const uint32_t tS = tmem_base + lane_off + w * 128;
+      const uint32_t tO = tmem_base + lane_off + 256 + w * 128;
+      const uint32_t sPw = sP + w * 2 * kTileBytes;
+      constexpr float c2 = kSoftmaxScale * kLog2e;
+      float acc[64];
+#pragma unroll
+      for (int k = 0; k < 64; ++k) acc[k] = 0.f;
+      float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
+      const int n_it = jmax[w] - jmin[w] + 1;
+      for (int i = 0; i < n_it; ++i) {
+        const int j = jmin[w] + i;
+        mbar_wait(bSfull(w), i & 1);
+        tc_fence_after();
+        const bool need_mask = (j * 128 + 127 > q0 + 128 * w) || (j * 128 < ds_hi);
+        const int key0 = j * 128;
+        // ---- pass 1: row max
+        float rmax = -INFINITY;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t sr[32];
+          tmem_ld_32x32b_x32(tS + c * 32, sr);
+          tmem_ld_wait();
+          if (need_mask) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+              const int key = key0 + c * 32 + k;
+              if (key <= t && key >= ds_t) rmax = fmaxf(rmax, __uint_as_float(sr[k]));
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) rmax = fmaxf(rmax, __uint_as_float(sr[k]));
+          }
+        }
+        const float m_new = fmaxf(m_run, rmax);
+        const float m_eff = (m_new == -INFINITY) ? 0.f : m_new;
+        const float alpha = ex2f((m_run - m_eff) * c2);  // m_run = -inf -> 0
+        const float mb = m_eff * c2;
+        // ---- pass 2: P = exp2(S*c2 - m*c2) -> bf16 -> shared memory (K-major, swizzled); row sum in fp32
+        float psum = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t sr[32];
+          tmem_ld_32x32b_x32(tS + c * 32, sr);
+          tmem_ld_wait();
+          float p[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            float e = ex2f(fmaf(__uint_as_float(sr[k]), c2, -mb));
+            if (need_mask) {
+              const int key = key0 + c * 32 + k;
+              if (!(key <= t && key >= ds_t)) e = 0.f;
+            }
+            p[k] = e;
+            psum += e;
+          }
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            uint4 o;
+            o.x = pack_bf16x2(p[v * 8 + 0], p[v * 8 + 1]);
+            o.y = pack_bf16x2(p[v * 8 + 2], p[v * 8 + 3]);
+            o.z = pack_bf16x2(p[v * 8 + 4], p[v * 8 + 5]);
+            o.w = pack_bf16x2(p[v * 8 + 6], p[v * 8 + 7]);
+            const int chunk = c * 4 + v;  // 16-byte chunk index within the 256-byte P row
+            st_shared_v4(sPw + (chunk >> 3) * kTileBytes + r * 128 + (((chunk & 7) ^ (r & 7)) << 4), o);
+          }
+        }
+        l_run = l_run * alpha + psum;
+        m_run = m_new;
+        tc_fence_before();
+        fence_proxy_async_smem();
+        mbar_arrive(bPfull(w));
+        // ---- fold the previous tile's P.V (already complete: its MMAs precede S_i in the tensor pipe)
+        if (i > 0) {
+          const int ob = (i - 1) & 1;
+          mbar_wait(bOfull(w, ob), ((i - 1) >> 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t orr[32];
+            tmem_ld_32x32b_x32(tO + ob * 64 + c * 32, orr);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 32; ++k) acc[c * 32 + k] = fmaf(acc[c * 32 + k], alpha_prev, __uint_as_float(orr[k]));
+          }
+        }
+        alpha_prev = alpha;
+      }
+      // ---- epilogue: last tile's P.V, normalise, store
+      {
+        const int ob = (n_it - 1) & 1;
+        mbar_wait(bOfull(w, ob), ((n_it - 1) >> 1) & 1);
+        tc_fence_after();
+        const float inv_l = 1.f / l_run;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t orr[32];
+          tmem_ld_32x32b_x32(tO + ob * 64 + c * 32, orr);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 32; ++k) acc[c * 32 + k] = fmaf(acc[c * 32 + k], alpha_prev, __uint_as_float(orr[k])) * inv_l;
+        }
+        if (t < T) {
+          __nv_bfloat16* orow = out + (seq_row0 + t) * d + h * 64;
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            uint4 o;
+            o.x = pack_bf16x2(acc[v * 8 + 0], acc[v * 8 + 1]);
+            o.y = pack_bf16x2(acc[v * 8 + 2], acc[v * 8 + 3]);
+            o.z = pack_bf16x2(acc[v * 8 + 4], acc[v * 8 + 5]);
+            o.w = pack_bf16x2(acc[v * 8 + 6], acc[v * 8 + 7]);
+            *reinterpret_cast<uint4*>(orow + v * 8) = o;
+          }
+          lse[(static_cast<long>(b) * NH + h) * T + t] = m_run * kSoftmaxScale + logf(l_run);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 11) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// ================================================================================================ backward
+// delta[b][h][t] = sum_c dout[b,t,h,c] * out[b,t,h,c]   (one warp per (token, head) pair would waste lanes: 8 lanes each)
+__global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
+                                     float* __restrict__ delta, int BT, int T, int NH) {
+  const long gid = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
+  const long item = gid >> 3;  // (row, head)
+  const int c = static_cast<int>(gid & 7);
+  if (item >= static_cast<long>(BT) * NH) return;
+  const long row = item / NH;
+  const int h = static_cast<int>(item % NH);
+  const long off = row * (NH * 64) + h * 64 + c * 8;
+  const uint4 a = ld_global_nc_v4(out + off), g = ld_global_nc_v4(dout + off);
+  const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 x = unpack_bf16x2(aw[k]), y = unpack_bf16x2(gw[k]);
+    s += x.x * y.x + x.y * y.y;
+  }
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  if (c == 0) {
+    const long bb = row / T;
+    const int t = static_cast<int>(row % T);
+    delta[(bb * NH + h) * T + t] = s;
+  }
+}
+
+struct AttnBwdSmem {
+  static constexpr int kK = 0;                      // K_j rotated
+  static constexpr int kV = kK + kTileBytes;        // V_j
+  static constexpr int kQ = kV + kTileBytes;        // 2 stages, rotated Q_i
+  static constexpr int kdO = kQ + 2 * kTileBytes;   // 2 stages
+  static constexpr int kP = kdO + 2 * kTileBytes;   // 128 x 128 bf16
+  static constexpr int kdS = kP + 2 * kTileBytes;   // 128 x 128 bf16
+  static constexpr int kBar = kdS + 2 * kTileBytes;
+  static constexpr int kBytes = kBar + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                const __nv_bfloat16* __restrict__ qkv, const float* __restrict__ cos_sin,
+                const int32_t* __restrict__ doc_start, const float* __restrict__ lse, const float* __restrict__ delta,
+                float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int T, int NH) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV, sQ = sbase + AttnBwdSmem::kQ,
+                 sdO = sbase + AttnBwdSmem::kdO, sP = sbase + AttnBwdSmem::kP, sdS = sbase + AttnBwdSmem::kdS,
+                 sBar = sbase + AttnBwdSmem::kBar;
+  const uint32_t bKready = sBar;                                // (128)
+  const uint32_t bVfull = sBar + 8;                             // (tx)
+  auto bQready = [&](int s) { return sBar + 8u * (2 + s); };    // [2] (128)
+  auto bdOfull = [&](int s) { return sBar + 8u * (4 + s); };    // [2] (tx)
+  auto bStageEmpty = [&](int s) { return sBar + 8u * (6 + s); };  // [2] (1, commit)
+  const uint32_t bSdPfull = sBar + 8u * 8;                      // (1, commit)
+  const uint32_t bPdSfull = sBar + 8u * 9;                      // (256)
+  const uint32_t bdQfull = sBar + 8u * 10;                      // (1, commit)
+  const uint32_t bdQempty = sBar + 8u * 11;                     // (256)
+  const uint32_t bAccFull = sBar + 8u * 12;                     // (1, commit) dK/dV complete
+  const uint32_t tmem_ptr_smem = sBar + 8u * 13;
+  volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int j = blockIdx.x;  // key tile
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int d = NH * 64, ld = 3 * d;
+  const long seq_row0 = static_cast<long>(b) * T;
+  const int n_qt = (T + 127) / 128;
+  const int key0 = j * 128;
+  // query tiles that can see this key tile: i >= j (causal) and doc_start[first row of tile i] <= last key of tile j
+  const int i_lo = j;
+  int i_hi = n_qt - 1;
+  if (doc_start) {
+    const int key_last = min(key0 + 127, T - 1);
+    // doc_start is non-decreasing in t: binary search the last tile whose first row's document starts <= key_last
+    int lo = j, hi = n_qt - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (doc_start[seq_row0 + mid * 128] <= key_last) lo = mid; else hi = mid - 1;
+    }
+    i_hi = lo;
+  }
+  const int n_it = i_hi - i_lo + 1;
+
+  if (warp == 12 && lane == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(bKready, 128);
+    mbar_init(bVfull, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bQready(s), 128);
+      mbar_init(bdOfull(s), 1);
+      mbar_init(bStageEmpty(s), 1);
+    }
+    mbar_init(bSdPfull, 1);
+    mbar_init(bPdSfull, 256);
+    mbar_init(bdQfull, 1);
+    mbar_init(bdQempty, 256);
+    mbar_init(bAccFull, 1);
+    fence_mbar_init();
+  }
+  if (warp == 11) tmem_alloc<512>(tmem_ptr_smem);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_generic;
+  const uint32_t tS = tmem_base, tdP = tmem_base + 128, tdV = tmem_base + 256, tdK = tmem_base + 320, tdQ = tmem_base + 384;
+
+  if (warp >= 8 && warp < 12) {
+    // ============================== loader warps ==============================
+    const int ltid = tid - 256;
+    if (ltid == 0) {
+      mbar_expect_tx(bVfull, kTileBytes);
+      tma_load_2d(sV, &tm_qkv, bVfull, 2 * d + h * 64, static_cast<int>(seq_row0) + key0);
+    }
+    load_rope_tile(sK, qkv + d + h * 64, ld, seq_row0 + key0, key0, T, cos_sin, ltid);
+    fence_proxy_async_smem();
+    mbar_arrive(bKready);
+    for (int it = 0; it < n_it; ++it) {
+      const int i = i_lo + it;
+      const int stage = it & 1;
+      mbar_wait(bStageEmpty(stage), ((it >> 1) & 1) ^ 1u);
+      if (ltid == 0) {
+        mbar_expect_tx(bdOfull(stage), kTileBytes);
+        tma_load_2d(sdO + stage * kTileBytes, &tm_do, bdOfull(stage), h * 64, static_cast<int>(seq_row0) + i * 128);
+      }
+      load_rope_tile(sQ + stage * kTileBytes, qkv + h * 64, ld, seq_row0 + i * 128, i * 128, T, cos_sin, ltid);
+      fence_proxy_async_smem();
+      mbar_arrive(bQready(stage));
+    }
+  } else if (warp == 12) {
+    // ============================== MMA issuer ==============================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);   // S, dP
+      constexpr uint32_t idesc_kv = umma_idesc_bf16(128, 64, true, true);     // dV = P^T.dO, dK = dS^T.Q
+      constexpr uint32_t idesc_dq = umma_idesc_bf16(128, 64, false, true);    // dQ = dS.K
+      mbar_wait(bKready, 0);
+      mbar_wait(bVfull, 0);
+      tc_fence_after();
+      auto issue_SdP = [&](int stage) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = umma_smem_desc(sQ + stage * kTileBytes + k * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sK + k * 32, 16, 1024);
+          umma_bf16_ss(tS, da, db, idesc_s, k > 0 ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t da = umma_smem_desc(sdO + stage * kTileBytes + k * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sV + k * 32, 16, 1024);
+          umma_bf16_ss(tdP, da, db, idesc_s, k > 0 ? 1u : 0u);
+        }
+        tc_commit(bSdPfull);
+      };
+      if (n_it > 0) {
+        mbar_wait(bQready(0), 0);
+        mbar_wait(bdOfull(0), 0);
+        tc_fence_after();
+        issue_SdP(0);
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int stage = it & 1;
+        mbar_wait(bPdSfull, it & 1);
+        mbar_wait(bdQempty, (it & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // contraction over the 128 query rows, 16 per step
+          // A = P^T (MN-major view of P[q][key]: two 64-key atoms 16 KB apart); B = dO (MN-major)
+          const uint64_t da = umma_smem_desc(sP + k * 2048, kTileBytes, 1024);
+          const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint64_t da = umma_smem_desc(sdS + k * 2048, kTileBytes, 1024);
+          const uint64_t db = umma_smem_desc(sQ + stage * kTileBytes + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tdK, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // contraction over the 128 keys
+          const uint64_t da = umma_smem_desc(sdS + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sK + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tdQ, da, db, idesc_dq, k > 0 ? 1u : 0u);
+        }
+        tc_commit(bdQfull);
+        tc_commit(bStageEmpty(stage));
+        if (it + 1 < n_it) {
+          const int s1 = (it + 1) & 1;
+          mbar_wait(bQready(s1), ((it + 1) >> 1) & 1);
+          mbar_wait(bdOfull(s1), ((it + 1) >> 1) & 1);
+          tc_fence_after();
+          issue_SdP(s1);
+        }
+      }
+      tc_commit(bAccFull);
+    }
+    __syncwarp();
+  } else {
+    // ============================== compute warps (256 threads: row r, column half `half`) ==============================
+    const int r = tid & 127;
+    const int half = tid >> 7;
+    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    constexpr float c2 = kSoftmaxScale * kLog2e;
+    for (int it = 0; it < n_it; ++it) {
+      const int i = i_lo + it;
+      const int t = i * 128 + r;
+      const long stat_idx = (static_cast<long>(b) * NH + h) * T + min(t, T - 1);
+      const float lse2 = lse[stat_idx] * kLog2e;
+      const float dlt = delta[stat_idx];
+      const int ds_t = doc_start ? doc_start[seq_row0 + min(t, T - 1)] : 0;
+      const bool need_mask = (key0 + 127 > i * 128) || (doc_start != nullptr);
+      mbar_wait(bSdPfull, it & 1);
+      tc_fence_after();
+      if (it > 0) {
+        // dQ of the previous query tile (its MMAs precede S/dP of this tile in the tensor pipe)
+        mbar_wait(bdQfull, (it - 1) & 1);
+        tc_fence_after();
+        uint32_t qr[32];
+        tmem_ld_32x32b_x32(tdQ + lane_off + half * 32, qr);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(bdQempty);
+        const int tp = (i - 1) * 128 + r;
+        if (tp < T) {
+          float* dst = dq_acc + (seq_row0 + tp) * d + h * 64 + half * 32;
+#pragma unroll
+          for (int v = 0; v < 8; ++v)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + v * 4), "f"(__uint_as_float(qr[v * 4 + 0])),
+                         "f"(__uint_as_float(qr[v * 4 + 1])), "f"(__uint_as_float(qr[v * 4 + 2])),
+                         "f"(__uint_as_float(qr[v * 4 + 3]))
+                         : "memory");
+        }
+      }
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        const int col0 = half * 64 + c * 32;
+        uint32_t sr[32], pr[32];
+        tmem_ld_32x32b_x32(tS + lane_off + col0, sr);
+        tmem_ld_32x32b_x32(tdP + lane_off + col0, pr);
+        tmem_ld_wait();
+        float p[32], ds[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          float e = ex2f(fmaf(__uint_as_float(sr[k]), c2, -lse2));
+          if (need_mask) {
+            const int key = key0 + col0 + k;
+            if (!(key <= t && key >= ds_t)) e = 0.f;
+          }
+          p[k] = e;
+          ds[k] = e * (__uint_as_float(pr[k]) - dlt) * kSoftmaxScale;
+        }
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          uint4 o, g;
+          o.x = pack_bf16x2(p[v * 8 + 0], p[v * 8 + 1]); o.y = pack_bf16x2(p[v * 8 + 2], p[v * 8 + 3]);
+          o.z = pack_bf16x2(p[v * 8 + 4], p[v * 8 + 5]); o.w = pack_bf16x2(p[v * 8 + 6], p[v * 8 + 7]);
+          g.x = pack_bf16x2(ds[v * 8 + 0], ds[v * 8 + 1]); g.y = pack_bf16x2(ds[v * 8 + 2], ds[v * 8 + 3]);
+          g.z = pack_bf16x2(ds[v * 8 + 4], ds[v * 8 + 5]); g.w = pack_bf16x2(ds[v * 8 + 6], ds[v * 8 + 7]);
+          const int chunk = (col0 >> 3) + v;
+          const uint32_t off = (chunk >> 3) * kTileBytes + r * 128 + (((chunk & 7) ^ (r & 7)) << 4);
+          st_shared_v4(sP + off, o);
+          st_shared_v4(sdS + off, g);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(bPdSfull);
+    }
+    // ---- tail: last dQ, then dK / dV
+    if (n_it > 0) {
+      mbar_wait(bdQfull, (n_it - 1) & 1);
+      tc_fence_after();
+      uint32_t qr[32];
+      tmem_ld_32x32b_x32(tdQ + lane_off + half * 32, qr);
+      tmem_ld_wait();
+      const int tp = i_hi * 128 + r;
+      if (tp < T) {
+        float* dst = dq_acc + (seq_row0 + tp) * d + h * 64 + half * 32;
+#pragma unroll
+        for (int v = 0; v < 8; ++v)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + v * 4), "f"(__uint_as_float(qr[v * 4 + 0])),
+                       "f"(__uint_as_float(qr[v * 4 + 1])), "f"(__uint_as_float(qr[v * 4 + 2])),
+                       "f"(__uint_as_float(qr[v * 4 + 3]))
+                       : "memory");
+      }
+      mbar_wait(bAccFull, 0);
+      tc_fence_after();
+      // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
+      uint32_t kr[32], vr[32];
+      tmem_ld_32x32b_x32(tdK + lane_off + half * 32, kr);
+      tmem_ld_32x32b_x32(tdV + lane_off + half * 32, vr);
+      tmem_ld_wait();
+      const int tk = key0 + r;
+      if (tk < T) {
+        __nv_bfloat16* krow = dqkv + (seq_row0 + tk) * ld + d + h * 64 + half * 32;
+        __nv_bfloat16* vrow = dqkv + (seq_row0 + tk) * ld + 2 * d + h * 64 + half * 32;
+        const float4* cs = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(tk) * 32 + half * 16) * 2);
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(vr[v * 8 + 0]), __uint_as_float(vr[v * 8 + 1]));
+          o.y = pack_bf16x2(__uint_as_float(vr[v * 8 + 2]), __uint_as_float(vr[v * 8 + 3]));
+          o.z = pack_bf16x2(__uint_as_float(vr[v * 8 + 4]), __uint_as_float(vr[v * 8 + 5]));
+          o.w = pack_bf16x2(__uint_as_float(vr[v * 8 + 6]), __uint_as_float(vr[v * 8 + 7]));
+          *reinterpret_cast<uint4*>(vrow + v * 8) = o;
+          // dK: transpose of the rotation, applied to the fp32 accumulators
+          const float4 c0 = __ldg(cs + 2 * v), c1 = __ldg(cs + 2 * v + 1);
+          const float g0 = __uint_as_float(kr[v * 8 + 0]), g1 = __uint_as_float(kr[v * 8 + 1]);
+          const float g2 = __uint_as_float(kr[v * 8 + 2]), g3 = __uint_as_float(kr[v * 8 + 3]);
+          const float g4 = __uint_as_float(kr[v * 8 + 4]), g5 = __uint_as_float(kr[v * 8 + 5]);
+          const float g6 = __uint_as_float(kr[v * 8 + 6]), g7 = __uint_as_float(kr[v * 8 + 7]);
+          uint4 q;
+          q.x = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
+          q.y = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
+          q.z = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
+          q.w = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
+          *reinterpret_cast<uint4*>(krow + v * 8) = q;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 11) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// dqkv[:, q columns] = bf16( R(-theta) . dq_acc )    (dq_acc fp32 [B*T][d])
+__global__ void attn_bwd_dq_post_kernel(const float* __restrict__ dq_acc, const float* __restrict__ cos_sin,
+                                        __nv_bfloat16* __restrict__ dqkv, long BT, int T, int d) {
+  const int vpr = d / 8;
+  const long total = BT * vpr;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const long row = i / vpr;
+    const int col = static_cast<int>(i % vpr) * 8;
+    const int t = static_cast<int>(row % T);
+    const int fc = (col & 63) >> 1;  // first frequency index of this chunk
+    const float4 a = *reinterpret_cast<const float4*>(dq_acc + row * d + col);
+    const float4 bq = *reinterpret_cast<const float4*>(dq_acc + row * d + col + 4);
+    const float4* cs = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(t) * 32 + fc) * 2);
+    const float4 c0 = __ldg(cs), c1 = __ldg(cs + 1);
+    uint4 o;
+    o.x = pack_bf16x2(a.x * c0.x + a.y * c0.y, a.y * c0.x - a.x * c0.y);
+    o.y = pack_bf16x2(a.z * c0.z + a.w * c0.w, a.w * c0.z - a.z * c0.w);
+    o.z = pack_bf16x2(bq.x * c1.x + bq.y * c1.y, bq.y * c1.x - bq.x * c1.y);
+    o.w = pack_bf16x2(bq.z * c1.z + bq.w * c1.w, bq.w * c1.z - bq.z * c1.w);
+    *reinterpret_cast<uint4*>(dqkv + row * 3 * d + col) = o;
+  }
+}
+
+}  // namespace pcv
+
+using namespace pcv;
+
+static int attn_check(int B, int T, int NH) {
+  if (B <= 0 || T <= 0 || NH <= 0) return PCV_ERR_ARG;
+  if (T % 128) return PCV_ERR_ARG;  // v1: whole 128-row tiles
+  return PCV_OK;
+}
+
+extern "C" int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, void* out, float* lse,
+                            int B, int T, int n_heads, void* stream) {
+  if (!qkv || !cos_sin || !out || !lse) return PCV_ERR_ARG;
+  int rc = attn_check(B, T, n_heads);
+  if (rc) return rc;
+  const int d = n_heads * 64;
+  CUtensorMap tm;
+  rc = get_tmap_2d_bf16(&tm, qkv, static_cast<uint64_t>(B) * T, 3 * d, 3 * d, 128);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnFwdSmem::kBytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr = true;
+  }
+  dim3 grid((T + 255) / 256, n_heads, B);
+  attn_fwd_kernel<<<grid, kAttnThreads, AttnFwdSmem::kBytes, static_cast<cudaStream_t>(stream)>>>(
+      tm, static_cast<const __nv_bfloat16*>(qkv), cos_sin, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
+  count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out,
+                            const void* dout, const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T,
+                            int n_heads, void* stream) {
+  if (!qkv || !cos_sin || !out || !dout || !lse || !delta || !dq_acc || !dqkv) return PCV_ERR_ARG;
+  int rc = attn_check(B, T, n_heads);
+  if (rc) return rc;
+  const int d = n_heads * 64;
+  const long BT = static_cast<long>(B) * T;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  CUtensorMap tm_qkv, tm_do;
+  rc = get_tmap_2d_bf16(&tm_qkv, qkv, BT, 3 * d, 3 * d, 128);
+  if (rc) return rc;
+  rc = get_tmap_2d_bf16(&tm_do, dout, BT, d, d, 128);
+  if (rc) return rc;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::kBytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr = true;
+  }
+  cudaError_t e = cudaMemsetAsync(dq_acc, 0, BT * d * sizeof(float), st);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  {
+    const long threads = BT * n_heads * 8;
+    attn_bwd_prep_kernel<<<static_cast<int>((threads + 255) / 256), 256, 0, st>>>(
+        static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, static_cast<int>(BT), T, n_heads);
+  }
+  dim3 grid(T / 128, n_heads, B);
+  attn_bwd_kernel<<<grid, kAttnThreads, AttnBwdSmem::kBytes, st>>>(
+      tm_qkv, tm_do, static_cast<const __nv_bfloat16*>(qkv), cos_sin, doc_start, lse, delta, dq_acc,
+      static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
+  {
+    const long total = BT * (d / 8);
+    long blocks = (total + 255) / 256;
+    const long cap = static_cast<long>(num_sms()) * 16;
+    if (blocks > cap) blocks = cap;
+    attn_bwd_dq_post_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(dq_acc, cos_sin, static_cast<__nv_bfloat16*>(dqkv), BT, T, d);
+  }
+  count_launch(3);
+  return cuda_rc();
+}

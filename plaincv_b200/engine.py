@@ -1,0 +1,188 @@
+"""Step functions ("engine") for the LM hot path: the torch-side equivalent of train_lm.py's
+compute_grads / eval_step (:189-313) and of its gradient-accumulation loop (:644-664), with the data-parallel
+exchange of `jax.lax.pmean(grads, "data")` (:207, :268) done as a bucketed NCCL all-reduce that overlaps backward.
+
+One process per GPU (torchrun).  Differences from the reference that are deliberate:
+  * the all-reduce runs once per optimizer step (on the last micro-batch), not on every micro-step;
+  * buckets are the per-layer slices of the model's flat fp32 gradient buffer, launched on a side stream as soon as a
+    block's backward has finished (reverse layer order), so NVLink traffic hides under the remaining backward;
+  * loss and accuracy are averaged in one extra 2-float all-reduce.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .batch import prepare_batch
+
+
+class GradReducer:
+    """Mean all-reduce of [begin, end) slices of one flat gradient buffer, one bucket at a time.
+
+    Device-agnostic on purpose: with CUDA tensors the collectives are issued on a dedicated communication stream
+    (fenced by events, so they overlap whatever the compute stream does next); with CPU tensors (gloo, used by the
+    world_size=2 tests) they are issued as async work handles."""
+
+    def __init__(self, flat_grad: torch.Tensor, ranges: Sequence[Tuple[int, int]], process_group=None):
+        self.flat = flat_grad
+        self.ranges = list(ranges)
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.cuda = flat_grad.is_cuda
+        self.comm_stream = torch.cuda.Stream(device=flat_grad.device) if (self.cuda and self.world > 1) else None
+        self._handles: List = []
+        self._launched: List[int] = []
+        backend = dist.get_backend(process_group) if self.world > 1 else None
+        self._avg_op = dist.ReduceOp.AVG if backend == "nccl" else None
+
+    def _all_reduce_mean(self, t: torch.Tensor, async_op: bool):
+        if self._avg_op is not None:
+            return dist.all_reduce(t, op=self._avg_op, group=self.pg, async_op=async_op)
+        work = dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.pg, async_op=async_op)
+        return (work, t)
+
+    def bucket_ready(self, idx: int) -> None:
+        """Call when every gradient inside bucket `idx` has been produced on the current stream."""
+        if self.world == 1:
+            return
+        self._launched.append(idx)
+        b, e = self.ranges[idx]
+        view = self.flat[b:e]
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                self._all_reduce_mean(view, async_op=False)
+        else:
+            self._handles.append(self._all_reduce_mean(view, async_op=True))
+
+    def reduce_scalars(self, t: torch.Tensor) -> None:
+        """Mean all-reduce of a small tensor (loss, acc) on the same path as the buckets."""
+        if self.world == 1:
+            return
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream())
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                self._all_reduce_mean(t, async_op=False)
+        else:
+            self._handles.append(self._all_reduce_mean(t, async_op=True))
+
+    def finish(self) -> None:
+        """Launch any bucket not yet launched, then make the compute stream wait for all of them."""
+        if self.world == 1:
+            return
+        for idx in range(len(self.ranges)):
+            if idx not in self._launched:
+                self.bucket_ready(idx)
+        self._launched = []
+        if self.cuda:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        else:
+            for h in self._handles:
+                if isinstance(h, tuple):
+                    work, t = h
+                    work.wait()
+                    t.div_(self.world)
+                elif h is not None:
+                    h.wait()
+            self._handles = []
+
+
+class Engine:
+    """compute_grads / eval_step / train_step over a plaincv_b200.Transformer."""
+
+    def __init__(self, model, seq_len: Optional[int] = None, use_doc_mask: bool = False, process_group=None,
+                 overlap: bool = True):
+        self.model = model
+        self.seq_len = int(seq_len if seq_len is not None else model.cfg.seq_len)
+        self.use_doc_mask = bool(use_doc_mask)
+        self.overlap = overlap
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        L = model.layout
+        # buckets in the order their gradients become final during backward: head, layers L-1..0, embedding
+        self._ranges = [L.head_range] + list(reversed(L.layer_ranges)) + [L.embed_range]
+        self.reducer = GradReducer(model.flat_grad, self._ranges, process_group)
+
+    # ------------------------------------------------------------------ hooks
+    def _arm_hooks(self, on: bool) -> None:
+        m = self.model
+        if on and self.world > 1 and self.overlap:
+            m.head.on_grads_ready = lambda: self.reducer.bucket_ready(0)
+            n = len(m.layers)
+            for i, layer in enumerate(m.layers):
+                layer.on_grads_ready = (lambda k=(1 + (n - 1 - i)): self.reducer.bucket_ready(k))
+        else:
+            m.head.on_grads_ready = None
+            for layer in m.layers:
+                layer.on_grads_ready = None
+
+    # ------------------------------------------------------------------ steps
+    def _to_device(self, batch: dict):
+        inputs, labels, doc_start = prepare_batch(batch, self.seq_len, self.use_doc_mask)
+        dev = self.model.flat_grad.device
+
+        def up(t):
+            if t is None:
+                return None
+            t = t.contiguous()
+            if not t.is_pinned():
+                t = t.pin_memory()
+            return t.to(dev, non_blocking=True)
+
+        return up(inputs), up(labels), up(doc_start)
+
+    def _micro(self, batch: dict, accumulate: bool, sync: bool, loss_scale: float, stat: torch.Tensor) -> None:
+        m = self.model
+        inputs, labels, doc_start = self._to_device(batch)
+        if not accumulate:
+            m.flat_grad.zero_()
+        self._arm_hooks(sync)
+        loss, acc = m.loss_and_acc(inputs, labels, doc_start=doc_start, loss_scale=loss_scale, unit_grad=True)
+        loss.backward()
+        stat[0] += loss.detach()
+        stat[1] += acc.detach()
+        if sync and self.world > 1:
+            self.reducer.reduce_scalars(stat)
+            self.reducer.finish()
+        self._arm_hooks(False)
+
+    def compute_grads(self, batch: dict, *, accumulate: bool = False, sync: bool = True, loss_scale: float = 1.0):
+        """One micro-batch of fwd + bwd (train_lm.py:256-271).  Gradients land in model.flat_grad (param.grad are views):
+        zeroed first unless `accumulate`; averaged over ranks when `sync` (with the all-reduce overlapping backward).
+        Returns (loss, acc) as 0-dim device tensors, rank-averaged when `sync`."""
+        stat = torch.zeros(2, dtype=torch.float32, device=self.model.flat_grad.device)
+        self._micro(batch, accumulate, sync, loss_scale, stat)
+        return stat[0], stat[1]
+
+    def train_step(self, micro_batches: Sequence[dict]):
+        """The accumulation loop of train_lm.py:644-664 for one optimizer step: mean of the micro-batch gradients,
+        rank-averaged — with a single all-reduce (issued during the last micro-batch's backward), where the reference
+        all-reduces on every micro-step.  Returns the mean (loss, acc) over micro-batches and ranks."""
+        n = len(micro_batches)
+        stat = torch.zeros(2, dtype=torch.float32, device=self.model.flat_grad.device)
+        for k, mb in enumerate(micro_batches):
+            self._micro(mb, accumulate=k > 0, sync=(k == n - 1), loss_scale=1.0 / n, stat=stat)
+        return stat[0] / n, stat[1] / n
+
+    @torch.no_grad()
+    def eval_step(self, batch: dict):
+        """train_lm.py:273-284: forward + loss/acc, rank-averaged."""
+        inputs, labels, doc_start = self._to_device(batch)
+        loss, acc = self.model.loss_and_acc(inputs, labels, doc_start=doc_start)
+        stat = torch.stack([loss, acc])
+        if self.world > 1:
+            dist.all_reduce(stat, op=dist.ReduceOp.SUM)
+            stat = stat / self.world
+        return stat[0], stat[1]
+
+    def after_optimizer_step(self) -> None:
+        """Refresh the bf16 compute copies of the parameters (one cast kernel over the flat buffer)."""
+        self.model.sync_compute_weights()
+
+    def grads(self) -> Dict[str, torch.Tensor]:
+        return self.model.export_flax_grads()

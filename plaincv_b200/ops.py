@@ -1,0 +1,363 @@
+"""Thin Python wrappers over the C ABI (one function per kernel launch) and the torch.autograd.Functions built on
+them.  Tensors are only used as device memory handles: every wrapper passes raw pointers + the current CUDA stream
+to libplaincv_b200.so.  No wrapper has a PyTorch/CPU fallback.
+
+Reference operations replaced (see include/plaincv_b200.h for the per-kernel citations):
+  nn.Dense fwd/dgrad/wgrad, nn.Embed, nn.RMSNorm (+ the residual add of Block), silu(gate)*up,
+  RoPE + jax.nn.dot_product_attention, optax softmax cross-entropy + argmax accuracy.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import PCV_EPI_BF16, PCV_EPI_F32, PCV_EPI_F32_ATOMIC, check
+
+_NUM_SMS = 148
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _req(t: torch.Tensor, dtype: torch.dtype, what: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{what}: plaincv_b200 kernels need CUDA tensors (there is no CPU fallback)")
+    if t.dtype != dtype:
+        raise TypeError(f"{what}: expected {dtype}, got {t.dtype}")
+
+
+# ------------------------------------------------------------------------------------------------ raw launches
+def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, M: int, N: int, K: int, lda: int, ldb: int, ldc: int,
+         a_mn: bool, b_mn: bool, epilogue: int, splits: int = 1, alpha: float = 1.0) -> None:
+    """C[M,N] (=|+=) alpha * sum_k A(m,k) B(n,k) on tcgen05 (pcv_gemm_bf16)."""
+    lib = _lib.load()
+    check(lib.pcv_gemm_bf16(a.data_ptr(), b.data_ptr(), c.data_ptr(), M, N, K, lda, ldb, ldc, int(a_mn), int(b_mn),
+                            epilogue, splits, alpha, _stream()), "pcv_gemm_bf16")
+
+
+def linear_fwd(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """y[M,Np] = x[M,K] @ w[K,Np]; w is the bf16 copy of a flax (in,out) kernel (row stride Np)."""
+    M, K = x.shape
+    Np = w.shape[1]
+    y = torch.empty((M, Np), dtype=torch.bfloat16, device=x.device)
+    gemm(x, w, y, M, Np, K, K, Np, Np, False, True, PCV_EPI_BF16)
+    return y
+
+
+def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
+    """dx[M,K] = dy[M,Np] @ w[K,Np]^T."""
+    M, Np = dy.shape
+    K = w.shape[0]
+    dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
+    gemm(dy, w, dx, M, K, Np, Np, Np, K, False, False, PCV_EPI_BF16, 1, alpha)
+    return dx
+
+
+def wgrad_splits(k_in: int, n_out: int, tokens: int) -> int:
+    tiles = ((k_in + 127) // 128) * ((n_out + 255) // 256)
+    kb = (tokens + 63) // 64
+    s = max(1, -(-2 * _NUM_SMS // tiles))
+    return max(1, min(s, kb // 8 if kb >= 8 else 1))
+
+
+def linear_wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, alpha: float = 1.0) -> None:
+    """dw[K,Np] (fp32) += x[M,K]^T @ dy[M,Np]  (split-K, red.add epilogue)."""
+    M, K = x.shape
+    Np = dy.shape[1]
+    gemm(x, dy, dw, K, Np, M, K, Np, Np, True, True, PCV_EPI_F32_ATOMIC, wgrad_splits(K, Np, M), alpha)
+
+
+def cast_pad_bf16(src: torch.Tensor, dst: torch.Tensor, rows: int, cols: int, src_ld: int, dst_ld: int) -> None:
+    lib = _lib.load()
+    check(lib.pcv_cast_pad_bf16(src.data_ptr(), dst.data_ptr(), rows, cols, src_ld, dst_ld, _stream()),
+          "pcv_cast_pad_bf16")
+
+
+def embed_fwd(ids: torch.Tensor, table_bf16: torch.Tensor, d: int) -> torch.Tensor:
+    M = ids.numel()
+    x = torch.empty((M, d), dtype=torch.bfloat16, device=ids.device)
+    check(_lib.load().pcv_embed_fwd(ids.data_ptr(), table_bf16.data_ptr(), x.data_ptr(), M, d, _stream()),
+          "pcv_embed_fwd")
+    return x
+
+
+def embed_bwd(ids: torch.Tensor, dx: torch.Tensor, dE: torch.Tensor, d: int, ldE: int) -> None:
+    check(_lib.load().pcv_embed_bwd(ids.data_ptr(), dx.data_ptr(), dE.data_ptr(), ids.numel(), d, ldE, _stream()),
+          "pcv_embed_bwd")
+
+
+def rmsnorm_residual_fwd(res_in: torch.Tensor, delta: Optional[torch.Tensor], scale: torch.Tensor, eps: float):
+    """-> (res_out, y, rstd); res_out is res_in itself when delta is None."""
+    M, d = res_in.shape
+    y = torch.empty_like(res_in)
+    rstd = torch.empty((M,), dtype=torch.float32, device=res_in.device)
+    res_out = torch.empty_like(res_in) if delta is not None else res_in
+    check(_lib.load().pcv_rmsnorm_residual_fwd(res_in.data_ptr(), _p(delta), scale.data_ptr(),
+                                               res_out.data_ptr() if delta is not None else None, y.data_ptr(),
+                                               rstd.data_ptr(), M, d, eps, _stream()), "pcv_rmsnorm_residual_fwd")
+    return res_out, y, rstd
+
+
+def rmsnorm_residual_bwd(dy: torch.Tensor, dres_out: Optional[torch.Tensor], res_out: torch.Tensor,
+                         scale: torch.Tensor, rstd: torch.Tensor, dscale: torch.Tensor) -> torch.Tensor:
+    M, d = dy.shape
+    dres_in = torch.empty_like(dy)
+    check(_lib.load().pcv_rmsnorm_residual_bwd(dy.data_ptr(), _p(dres_out), res_out.data_ptr(), scale.data_ptr(),
+                                               rstd.data_ptr(), dres_in.data_ptr(), dscale.data_ptr(), M, d,
+                                               _stream()), "pcv_rmsnorm_residual_bwd")
+    return dres_in
+
+
+def swiglu_fwd(gu: torch.Tensor) -> torch.Tensor:
+    M, two_h = gu.shape
+    h = torch.empty((M, two_h // 2), dtype=torch.bfloat16, device=gu.device)
+    check(_lib.load().pcv_swiglu_fwd(gu.data_ptr(), h.data_ptr(), M, two_h // 2, _stream()), "pcv_swiglu_fwd")
+    return h
+
+
+def swiglu_bwd(gu: torch.Tensor, dh: torch.Tensor) -> torch.Tensor:
+    M, two_h = gu.shape
+    dgu = torch.empty_like(gu)
+    check(_lib.load().pcv_swiglu_bwd(gu.data_ptr(), dh.data_ptr(), dgu.data_ptr(), M, two_h // 2, _stream()),
+          "pcv_swiglu_bwd")
+    return dgu
+
+
+def attn_fwd(qkv: torch.Tensor, cos_sin: torch.Tensor, doc_start: Optional[torch.Tensor], B: int, T: int,
+             n_heads: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    d = n_heads * 64
+    out = torch.empty((B * T, d), dtype=torch.bfloat16, device=qkv.device)
+    lse = torch.empty((B, n_heads, T), dtype=torch.float32, device=qkv.device)
+    check(_lib.load().pcv_attn_fwd(qkv.data_ptr(), cos_sin.data_ptr(), _p(doc_start), out.data_ptr(), lse.data_ptr(),
+                                   B, T, n_heads, _stream()), "pcv_attn_fwd")
+    return out, lse
+
+
+def attn_bwd(qkv: torch.Tensor, cos_sin: torch.Tensor, doc_start: Optional[torch.Tensor], out: torch.Tensor,
+             dout: torch.Tensor, lse: torch.Tensor, B: int, T: int, n_heads: int) -> torch.Tensor:
+    d = n_heads * 64
+    dqkv = torch.empty_like(qkv)
+    delta = torch.empty((B, n_heads, T), dtype=torch.float32, device=qkv.device)
+    dq_acc = torch.empty((B * T, d), dtype=torch.float32, device=qkv.device)
+    check(_lib.load().pcv_attn_bwd(qkv.data_ptr(), cos_sin.data_ptr(), _p(doc_start), out.data_ptr(), dout.data_ptr(),
+                                   lse.data_ptr(), delta.data_ptr(), dq_acc.data_ptr(), dqkv.data_ptr(), B, T, n_heads,
+                                   _stream()), "pcv_attn_bwd")
+    return dqkv
+
+
+def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, V: int, grad_scale: float, write_grad: bool):
+    """-> (out2 = [mean loss, mean acc] fp32 device tensor, dlogits or None).  dlogits overwrites `logits`."""
+    M, ldl = logits.shape
+    row_loss = torch.empty((M,), dtype=torch.float32, device=logits.device)
+    row_correct = torch.empty((M,), dtype=torch.float32, device=logits.device)
+    lib = _lib.load()
+    check(lib.pcv_softmax_ce(logits.data_ptr(), labels.data_ptr(), logits.data_ptr() if write_grad else None,
+                             row_loss.data_ptr(), row_correct.data_ptr(), M, V, ldl, grad_scale, _stream()),
+          "pcv_softmax_ce")
+    out2 = torch.empty((2,), dtype=torch.float32, device=logits.device)
+    check(lib.pcv_mean2(row_loss.data_ptr(), row_correct.data_ptr(), out2.data_ptr(), M, _stream()), "pcv_mean2")
+    return out2, (logits if write_grad else None)
+
+
+def rope_table(head_dim: int, seq_len: int, theta: float, device) -> torch.Tensor:
+    """cos/sin table [T][hd/2][2] fp32, computed exactly as precompute_freqs_cis (models/LM/embedding.py:8-26) does:
+    a one-off host-side constant, uploaded once."""
+    if head_dim % 2 != 0:
+        raise ValueError("dim must be even (pairs of real/imag).")
+    inv_freqs = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
+    t = torch.arange(seq_len, dtype=torch.float32)
+    freqs = torch.outer(t, inv_freqs).to(torch.float32)
+    return torch.stack([torch.cos(freqs), torch.sin(freqs)], dim=-1).contiguous().to(device)
+
+
+# ------------------------------------------------------------------------------------------------ autograd: per op
+class LinearFn(torch.autograd.Function):
+    """y = x @ W for a flax (in,out) kernel.  `w_bf16` is the padded bf16 copy [K, Np]; the weight gradient is
+    accumulated straight into `w_grad` (fp32 [K, Np], the parameter's slot of the flat gradient buffer)."""
+
+    @staticmethod
+    def forward(ctx, x, w_bf16, w_grad):
+        ctx.save_for_backward(x, w_bf16)
+        ctx.w_grad = w_grad
+        return linear_fwd(x, w_bf16)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = linear_dgrad(dy, w)
+        if ctx.w_grad is not None:
+            linear_wgrad(x, dy, ctx.w_grad)
+        return dx, None, None
+
+
+class RMSNormFn(torch.autograd.Function):
+    """y = rmsnorm(x) * scale (fp32 statistics, bf16 out); dscale accumulates into `scale_grad`."""
+
+    @staticmethod
+    def forward(ctx, x, scale, scale_grad, eps):
+        _, y, rstd = rmsnorm_residual_fwd(x, None, scale, eps)
+        ctx.save_for_backward(x, scale, rstd)
+        ctx.scale_grad = scale_grad
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, scale, rstd = ctx.saved_tensors
+        return rmsnorm_residual_bwd(dy.contiguous(), None, x, scale, rstd, ctx.scale_grad), None, None, None
+
+
+class RMSNormResidualFn(torch.autograd.Function):
+    """(res_out, y) = (res + delta, rmsnorm(res + delta) * scale); dscale accumulates into `scale_grad`."""
+
+    @staticmethod
+    def forward(ctx, res, delta, scale, scale_grad, eps):
+        res_out, y, rstd = rmsnorm_residual_fwd(res, delta, scale, eps)
+        ctx.save_for_backward(res_out, scale, rstd)
+        ctx.scale_grad = scale_grad
+        return res_out, y
+
+    @staticmethod
+    def backward(ctx, dres_out, dy):
+        res_out, scale, rstd = ctx.saved_tensors
+        dres_in = rmsnorm_residual_bwd(dy.contiguous(), None if dres_out is None else dres_out.contiguous(), res_out,
+                                       scale, rstd, ctx.scale_grad)
+        return dres_in, dres_in, None, None, None
+
+
+class SwiGLUFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, gu):
+        ctx.save_for_backward(gu)
+        return swiglu_fwd(gu)
+
+    @staticmethod
+    def backward(ctx, dh):
+        (gu,) = ctx.saved_tensors
+        return swiglu_bwd(gu, dh.contiguous())
+
+
+class AttentionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, cos_sin, doc_start, B, T, n_heads):
+        out, lse = attn_fwd(qkv, cos_sin, doc_start, B, T, n_heads)
+        ctx.save_for_backward(qkv, out, lse, cos_sin, doc_start if doc_start is not None else torch.empty(0))
+        ctx.has_doc = doc_start is not None
+        ctx.dims = (B, T, n_heads)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse, cos_sin, doc_start = ctx.saved_tensors
+        B, T, n_heads = ctx.dims
+        dqkv = attn_bwd(qkv, cos_sin, doc_start if ctx.has_doc else None, out, dout.contiguous(), lse, B, T, n_heads)
+        return dqkv, None, None, None, None, None
+
+
+class EmbedFn(torch.autograd.Function):
+    """x = bf16(E)[ids].  `table` (the fp32 master parameter) only anchors the autograd graph; the gradient is
+    scatter-added into `table_grad` directly."""
+
+    @staticmethod
+    def forward(ctx, table, ids, table_bf16, table_grad, d, ldE):
+        ctx.save_for_backward(ids)
+        ctx.table_grad, ctx.d, ctx.ldE = table_grad, d, ldE
+        return embed_fwd(ids, table_bf16, d)
+
+    @staticmethod
+    def backward(ctx, dx):
+        (ids,) = ctx.saved_tensors
+        embed_bwd(ids, dx.contiguous(), ctx.table_grad, ctx.d, ctx.ldE)
+        return None, None, None, None, None, None
+
+
+# ------------------------------------------------------------------------------------------------ autograd: fused
+class BlockFn(torch.autograd.Function):
+    """One pre-norm decoder block (models/LM/transformer.py:260-335), hand-scheduled forward and backward.
+
+    Inputs (res, delta): the residual stream entering the block is res + delta (delta = previous block's MLP output,
+    None for the first block); the add is fused into the first RMSNorm.  Outputs (res2, m): residual stream after
+    the attention branch and the MLP branch output, to be added by the next block / the head.  `layer` carries the
+    bf16 weight copies, the fp32 norm scales and the gradient slots (see model._LayerHandles)."""
+
+    @staticmethod
+    def forward(ctx, res, delta, layer, rt):
+        eps = rt.eps
+        res1, h1, rstd1 = rmsnorm_residual_fwd(res, delta, layer.attn_norm, eps)
+        qkv = linear_fwd(h1, layer.w_qkv)
+        o, lse = attn_fwd(qkv, rt.cos_sin, rt.doc_start, rt.B, rt.T, rt.n_heads)
+        a = linear_fwd(o, layer.w_out)
+        res2, h2, rstd2 = rmsnorm_residual_fwd(res1, a, layer.mlp_norm, eps)
+        del a
+        gu = linear_fwd(h2, layer.w_gu)
+        hh = swiglu_fwd(gu)
+        m = linear_fwd(hh, layer.w_down)
+        ctx.save_for_backward(res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh)
+        ctx.layer, ctx.rt, ctx.has_delta = layer, rt, delta is not None
+        return res2, m
+
+    @staticmethod
+    def backward(ctx, d_res2, d_m):
+        res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh = ctx.saved_tensors
+        layer, rt = ctx.layer, ctx.rt
+        d_m = d_m.contiguous()
+        # MLP branch
+        d_hh = linear_dgrad(d_m, layer.w_down)
+        linear_wgrad(hh, d_m, layer.g_down)
+        d_gu = swiglu_bwd(gu, d_hh)
+        del d_hh
+        d_h2 = linear_dgrad(d_gu, layer.w_gu)
+        linear_wgrad(h2, d_gu, layer.g_gu)
+        del d_gu
+        d_r2 = rmsnorm_residual_bwd(d_h2, d_res2, res2, layer.mlp_norm, rstd2, layer.g_mlp_norm)
+        del d_h2
+        # attention branch
+        d_o = linear_dgrad(d_r2, layer.w_out)
+        linear_wgrad(o, d_r2, layer.g_out)
+        d_qkv = attn_bwd(qkv, rt.cos_sin, rt.doc_start, o, d_o, lse, rt.B, rt.T, rt.n_heads)
+        del d_o
+        d_h1 = linear_dgrad(d_qkv, layer.w_qkv)
+        linear_wgrad(h1, d_qkv, layer.g_qkv)
+        del d_qkv
+        d_r1 = rmsnorm_residual_bwd(d_h1, d_r2, res1, layer.attn_norm, rstd1, layer.g_attn_norm)
+        if layer.on_grads_ready is not None:
+            layer.on_grads_ready()
+        return d_r1, (d_r1 if ctx.has_delta else None), None, None
+
+
+class HeadLossFn(torch.autograd.Function):
+    """out_norm -> lm_head -> softmax cross-entropy + accuracy (transformer.py:384-405, train_lm.py:181-186).
+    Returns a 2-vector [loss, acc].  d(logits) is produced in the forward pass, in place of the bf16 logits, so the
+    fp32 [M,V] logits of the reference are never materialised."""
+
+    @staticmethod
+    def forward(ctx, res, delta, labels, head, rt, loss_scale, unit_grad):
+        res_f, hf, rstd = rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
+        logits = linear_fwd(hf, head.w_lm)
+        M = logits.shape[0]
+        need_grad = torch.is_grad_enabled() and res.requires_grad
+        out2, dlogits = softmax_ce(logits, labels, head.vocab, loss_scale / M, need_grad)
+        if need_grad:
+            ctx.save_for_backward(res_f, rstd, hf, dlogits)
+        ctx.head, ctx.has_delta, ctx.unit_grad = head, delta is not None, unit_grad
+        return out2
+
+    @staticmethod
+    def backward(ctx, g_out):
+        res_f, rstd, hf, dlogits = ctx.saved_tensors
+        head = ctx.head
+        alpha = 1.0 if ctx.unit_grad else float(g_out[0])
+        d_hf = linear_dgrad(dlogits, head.w_lm, alpha)
+        linear_wgrad(hf, dlogits, head.g_lm, alpha)
+        d_r = rmsnorm_residual_bwd(d_hf, None, res_f, head.out_norm, rstd, head.g_out_norm)
+        if head.on_grads_ready is not None:
+            head.on_grads_ready()
+        return d_r, (d_r if ctx.has_delta else None), None, None, None, None, None

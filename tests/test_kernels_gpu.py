@@ -1,0 +1,197 @@
+"""Per-kernel parity: each CUDA entry point (called through the C ABI via plaincv_b200.ops) against the CPU oracle on
+the same seeded inputs.  Tolerances: bf16 kernels vs the fp32 oracle evaluated on the same bf16-rounded inputs —
+relative L2 <= 1e-2 (the north star's gradient tolerance), fp32 outputs tighter where stated."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import lm_oracle as O  # noqa: E402  (test infrastructure: the checker)
+
+
+def rel_l2(a: torch.Tensor, b: torch.Tensor) -> float:
+    a = a.detach().double().cpu()
+    b = b.detach().double().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from plaincv_b200 import ops as _ops
+    return _ops
+
+
+def _bf(x):
+    return x.to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,K,N", [(256, 256, 768), (512, 768, 2048), (384, 1024, 2736), (1024, 256, 1368)])
+def test_linear_fwd_dgrad_wgrad(ops, M, K, N):
+    g = torch.Generator().manual_seed(0)
+    x = _bf(torch.randn(M, K, generator=g))
+    w = _bf(torch.randn(K, N, generator=g) * 0.05)
+    dy = _bf(torch.randn(M, N, generator=g))
+    xd, wd, dyd = x.cuda(), w.cuda(), dy.cuda()
+    y = ops.linear_fwd(xd, wd)
+    assert rel_l2(y, x.float() @ w.float()) < 1e-2
+    dx = ops.linear_dgrad(dyd, wd)
+    assert rel_l2(dx, dy.float() @ w.float().t()) < 1e-2
+    dw0 = torch.randn(K, N, generator=g)
+    dwd = dw0.cuda()
+    ops.linear_wgrad(xd, dyd, dwd)
+    assert rel_l2(dwd, dw0 + x.float().t() @ dy.float()) < 1e-4  # fp32 accumulate-in-place (split-K red.add)
+
+
+def test_cast_pad(ops):
+    g = torch.Generator().manual_seed(1)
+    src = torch.randn(37, 2730, generator=g)
+    dst = torch.full((37, 2736), 7.0, dtype=torch.bfloat16).cuda()
+    ops.cast_pad_bf16(src.cuda(), dst, 37, 2730, 2730, 2736)
+    out = dst.cpu()
+    assert torch.equal(out[:, :2730], src.to(torch.bfloat16))  # bit-exact round-to-nearest-even
+    assert torch.equal(out[:, 2730:], torch.zeros(37, 6, dtype=torch.bfloat16))
+
+
+def test_embed_fwd_bwd(ops):
+    g = torch.Generator().manual_seed(2)
+    V, d, M = 1000, 256, 777
+    table = _bf(torch.randn(V, d, generator=g))
+    ids = torch.randint(0, V, (M,), generator=g, dtype=torch.int32)
+    ids[:50] = 3  # collisions: many rows scatter into the same table row
+    x = ops.embed_fwd(ids.cuda(), table.cuda(), d)
+    assert torch.equal(x.cpu(), table[ids.long()])  # a gather is bit-exact
+    dx = _bf(torch.randn(M, d, generator=g))
+    dE = torch.zeros(V, d).cuda()
+    ops.embed_bwd(ids.cuda(), dx.cuda(), dE, d, d)
+    want = torch.zeros(V, d).index_add_(0, ids.long(), dx.float())
+    assert rel_l2(dE, want) < 1e-5
+
+
+@pytest.mark.parametrize("M,d", [(2048, 256), (1024, 768), (4096, 1024)])
+@pytest.mark.parametrize("with_delta", [False, True])
+def test_rmsnorm_residual(ops, M, d, with_delta):
+    g = torch.Generator().manual_seed(3)
+    res = _bf(torch.randn(M, d, generator=g))
+    delta = _bf(torch.randn(M, d, generator=g)) if with_delta else None
+    scale = 1.0 + 0.1 * torch.randn(d, generator=g)
+    eps = 1e-6
+    res_out, y, rstd = ops.rmsnorm_residual_fwd(res.cuda(), None if delta is None else delta.cuda(), scale.cuda(), eps)
+    r = res if delta is None else _bf(res.float() + delta.float())
+    if with_delta:
+        assert torch.equal(res_out.cpu(), r)  # residual stream: bf16(res + delta), bit-exact
+    r32 = r.float().requires_grad_(True)
+    sc = scale.clone().requires_grad_(True)
+    y_ref = O.rmsnorm(r32, sc, eps, torch.float32)
+    assert rel_l2(y, y_ref) < 4e-3
+    ms = (r.float() ** 2).mean(-1)
+    assert rel_l2(rstd, torch.rsqrt(ms + eps)) < 1e-5
+    # backward
+    dy = _bf(torch.randn(M, d, generator=g))
+    dres_out = _bf(torch.randn(M, d, generator=g))
+    y_ref.backward(dy.float())
+    dscale = torch.zeros(d).cuda()
+    dres_in = ops.rmsnorm_residual_bwd(dy.cuda(), dres_out.cuda(), res_out, scale.cuda(), rstd, dscale)
+    assert rel_l2(dres_in, r32.grad + dres_out.float()) < 5e-3
+    assert rel_l2(dscale, sc.grad) < 1e-3
+
+
+@pytest.mark.parametrize("M,hid", [(512, 2736), (1024, 2048), (256, 688)])
+def test_swiglu(ops, M, hid):
+    g = torch.Generator().manual_seed(4)
+    gu = _bf(torch.randn(M, 2 * hid, generator=g) * 2)
+    dh = _bf(torch.randn(M, hid, generator=g))
+    h = ops.swiglu_fwd(gu.cuda())
+    gu32 = gu.float().requires_grad_(True)
+    ref = O.silu(gu32[:, :hid]) * gu32[:, hid:]
+    assert rel_l2(h, ref) < 4e-3
+    ref.backward(dh.float())
+    dgu = ops.swiglu_bwd(gu.cuda(), dh.cuda())
+    assert rel_l2(dgu, gu32.grad) < 5e-3
+
+
+def _attention_oracle(qkv, B, T, NH, theta, doc_start=None):
+    """RoPE + attention on bf16-rounded qkv with the oracle's fp32 functions (autograd-enabled)."""
+    d = NH * 64
+    qkv3 = qkv.view(B, T, 3 * d)
+    q, k, v = torch.split(qkv3, d, dim=-1)
+    q = q.reshape(B, T, NH, 64)
+    k = k.reshape(B, T, NH, 64)
+    v = v.reshape(B, T, NH, 64)
+    freqs = O.precompute_freqs_cis(64, T, theta)
+    q, k = O.apply_rotary_emb_complex_like(q, k, freqs)
+    if doc_start is None:
+        out = O.dot_product_attention(q, k, v, None, True)
+    else:
+        s = torch.arange(T)
+        mask = (s[None, None, :] >= doc_start[:, :, None]) & (s[None, None, :] <= s[None, :, None])
+        out = O.dot_product_attention(q, k, v, mask[:, None], False)
+    return out.reshape(B * T, d)
+
+
+def _doc_starts(B, T, seed, mean):
+    batch = O.synthetic_batch(B, T, 100, seed=seed, doc_mean=mean)
+    from plaincv_b200.batch import doc_lengths_to_doc_start
+    return torch.from_numpy(doc_lengths_to_doc_start(batch["docs_lengths"], T))
+
+
+@pytest.mark.parametrize("B,T,NH,doc_mean", [(2, 256, 4, None), (1, 1024, 2, None), (2, 512, 3, 150), (1, 1024, 2, 40),
+                                             (1, 128, 1, None), (2, 384, 2, 1000)])
+def test_attention_fwd_bwd(ops, B, T, NH, doc_mean):
+    g = torch.Generator().manual_seed(5)
+    d = NH * 64
+    theta = 500000.0
+    qkv = _bf(torch.randn(B * T, 3 * d, generator=g))
+    dout = _bf(torch.randn(B * T, d, generator=g))
+    doc_start = _doc_starts(B, T, 11, doc_mean) if doc_mean else None
+    cos_sin = ops.rope_table(64, T, theta, "cuda")
+    ds_dev = None if doc_start is None else doc_start.to(torch.int32).cuda().view(-1)
+    out, lse = ops.attn_fwd(qkv.cuda(), cos_sin, ds_dev, B, T, NH)
+    torch.cuda.synchronize()
+    qkv32 = qkv.float().requires_grad_(True)
+    ref = _attention_oracle(qkv32, B, T, NH, theta, doc_start)
+    assert rel_l2(out, ref) < 1e-2, "attention forward"
+    ref.backward(dout.float())
+    dqkv = ops.attn_bwd(qkv.cuda(), cos_sin, ds_dev, out, dout.cuda(), lse, B, T, NH)
+    torch.cuda.synchronize()
+    gref = qkv32.grad
+    for name, sl in (("dq", slice(0, d)), ("dk", slice(d, 2 * d)), ("dv", slice(2 * d, 3 * d))):
+        assert rel_l2(dqkv[:, sl], gref[:, sl]) < 1.5e-2, f"attention backward {name}"
+
+
+def test_attention_first_row_is_v0(ops):
+    """Closed form: causal row 0 attends only to itself -> out[0] = v[0] (and doc starts behave the same)."""
+    g = torch.Generator().manual_seed(6)
+    B, T, NH = 1, 128, 2
+    d = NH * 64
+    qkv = _bf(torch.randn(B * T, 3 * d, generator=g))
+    cos_sin = ops.rope_table(64, T, 500000.0, "cuda")
+    ds = torch.arange(T, dtype=torch.int32).cuda()  # every token its own document
+    out, _ = ops.attn_fwd(qkv.cuda(), cos_sin, ds, B, T, NH)
+    assert torch.equal(out.cpu(), qkv[:, 2 * d:])  # each row returns exactly its own v
+
+
+@pytest.mark.parametrize("M,V", [(256, 50257), (512, 50280), (128, 1000)])
+def test_softmax_ce(ops, M, V):
+    g = torch.Generator().manual_seed(7)
+    ldl = (V + 7) // 8 * 8
+    logits = _bf(torch.randn(M, ldl, generator=g) * 3)
+    labels = torch.randint(0, V, (M,), generator=g, dtype=torch.int32)
+    logits[5, labels[5]] = 40.0  # a confidently-correct row
+    l32 = logits[:, :V].float().requires_grad_(True)
+    loss_ref, acc_ref = O.loss_and_acc(l32, labels)
+    loss_ref.backward()
+    buf = logits.cuda().clone()
+    out2, dlog = ops.softmax_ce(buf, labels.cuda(), V, 1.0 / M, True)
+    out2 = out2.cpu()
+    assert abs(float(out2[0]) - float(loss_ref)) / float(loss_ref) < 1e-5
+    assert float(out2[1]) == pytest.approx(float(acc_ref), abs=1e-7)
+    assert rel_l2(dlog[:, :V], l32.grad) < 4e-3
+    if ldl > V:
+        assert float(dlog[:, V:].abs().max()) == 0.0
+    # uniform logits: loss = ln V (closed form)
+    buf = torch.zeros(M, ldl, dtype=torch.bfloat16).cuda()
+    out2, _ = ops.softmax_ce(buf, labels.cuda(), V, 1.0, False)
+    assert float(out2[0]) == pytest.approx(math.log(V), rel=1e-6)
