@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py — train tokens/s (fwd + bwd [+ data-parallel gradient all-reduce]) of the models/LM causal Transformer.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c3] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json metric, config C3): the 420M LM of config/tr_420M_x8gpu.yaml (24 layers, d=1024, 16 heads,
+hid=2730, vocab 50280, seq 2048), per-GPU micro-batch 8 x 2048 tokens, bf16 compute / fp32 masters, synthetic
+uniform tokens, random-init weights.  One "step" = zero grads, bf16 weight refresh, forward, backward and (N>1) the
+bucketed gradient all-reduce.  Prints ONE JSON line on rank 0.
+
+`value`  : tokens/s with the token ids already resident in HBM (CUDA events, max over ranks).
+`e2e`    : the same through Engine.compute_grads(batch) with HOST (pinned) token ids, H2D copy and a D2H read of the
+           loss inside the timed region every step.
+`roofline`: the dominant kernel (the tcgen05 GEMM): model GEMM FLOPs of one step / the CUDA-event time of exactly that
+           GEMM sequence replayed back to back, against MEASURED_PEAKS.json's sustained bf16 figure.
+`cpu_baseline` / `--impl reference`: the reference's JAX path cannot run here (jax is not installed); the timed CPU
+           arm is the oracle port (oracle/lm_oracle.py, plain PyTorch fp32) on the host cores, on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (n_layers, d_model, n_heads, vocab, seq_len, per-GPU micro-batch, doc-masked)
+    "c1": dict(n_layers=4, d_model=256, n_heads=4, vocab_size=50257, seq_len=256, micro_batch=8, doc=False),
+    "c2": dict(n_layers=12, d_model=768, n_heads=12, vocab_size=50257, seq_len=1024, micro_batch=16, doc=False),
+    "c3": dict(n_layers=24, d_model=1024, n_heads=16, vocab_size=50280, seq_len=2048, micro_batch=8, doc=False),
+    "c4": dict(n_layers=24, d_model=1024, n_heads=16, vocab_size=50280, seq_len=4096, micro_batch=4, doc=False),
+    "c5": dict(n_layers=12, d_model=768, n_heads=12, vocab_size=50280, seq_len=2048, micro_batch=8, doc=True),
+}
+WORKLOAD_NAMES = {
+    "c1": "tiny LM 4L d256 seq256",
+    "c2": "GPT-2-small-sized LM 12L d768 seq1024",
+    "c3": "420M LM config/tr_420M_x8gpu.yaml 24L d1024 seq2048",
+    "c4": "420M LM long-context seq4096",
+    "c5": "doc-masked LM config/config_doc_mask.yaml 12L d768 seq2048",
+}
+
+
+def yaml_like_cfg(c: dict) -> dict:
+    """The reference's YAML keys (config/tr_420M_x8gpu.yaml) for construct_model."""
+    return dict(model="transformer", vocab_size=c["vocab_size"], d_model=c["d_model"], expand="8/3",
+                n_layers=c["n_layers"], n_heads=c["n_heads"], mlp_class="glu", seq_len=c["seq_len"],
+                tie_embeddings=False, dtype="bfloat16", seed=100)
+
+
+def flops_per_token(c: dict) -> float:
+    """6*(L*(4d^2 + 3*d*hid) + d*V) + 6*L*T*d  (un-padded dims, causal attention at half)."""
+    d, L, V, T = c["d_model"], c["n_layers"], c["vocab_size"], c["seq_len"]
+    hid = int(8 / 3 * d)
+    return 6.0 * (L * (4 * d * d + 3 * d * hid) + d * V) + 6.0 * L * T * d
+
+
+def gemm_flops_per_token(c: dict) -> float:
+    d, L, V = c["d_model"], c["n_layers"], c["vocab_size"]
+    hid = int(8 / 3 * d)
+    return 6.0 * (L * (4 * d * d + 3 * d * hid) + d * V)
+
+
+def load_peaks() -> dict:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        d["_source"] = "measured (MEASURED_PEAKS.json)"
+        return d
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0,
+            "_source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi SM clocks / throttle reasons for one GPU while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._t is not None:
+            self._t.join(timeout=6)
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                smax.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm (oracle)
+def run_cpu_arm(cname: str, steps: int, warmup: int, max_seconds: float = 150.0) -> dict:
+    """Times the oracle port (the only runnable form of the reference's CPU path here) on the host cores:
+    fwd + bwd of the same model on a bounded sample (ONE sequence of the config), all host threads."""
+    import torch
+    from oracle import lm_oracle as O
+    c = CONFIGS[cname]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = O.ModelConfig(vocab_size=c["vocab_size"], seq_len=c["seq_len"], dim=c["d_model"], expand=8 / 3,
+                        n_layers=c["n_layers"], n_heads=c["n_heads"])
+    params = O.init_params(cfg, seed=0)
+    B = 1
+    batch = O.synthetic_batch(B, c["seq_len"], c["vocab_size"], seed=1234, doc_mean=512 if c["doc"] else None)
+    inputs, labels, mask = O.prepare_batch(batch, c["seq_len"], c["doc"])
+    times = []
+    t_begin = time.perf_counter()
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        O.compute_grads(params, cfg, inputs, labels, mask, torch.float32)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+        if time.perf_counter() - t_begin > max_seconds and len(times) >= 1:
+            break
+    ms = 1e3 * sum(times) / len(times)
+    tokens = B * c["seq_len"]
+    return {"value": tokens / (ms / 1e3), "unit": "tokens/s", "cores": cores, "kind": "port",
+            "sample": f"oracle/lm_oracle.py fp32 fwd+bwd, {B} sequence x {c['seq_len']} tokens of {cname}, "
+                      f"{len(times)} timed step(s) after {warmup} warm-up",
+            "ms_per_step": ms, "steps": len(times)}
+
+
+def reference_main(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    c = CONFIGS[args.config]
+    cb = run_cpu_arm(args.config, max(1, min(args.steps, 5)), max(0, min(args.warmup, 1)))
+    line = {
+        "impl": "reference", "metric": "train tokens/s fwd+bwd", "value": cb["value"], "unit": "tokens/s",
+        "n_gpus": args.gpus, "steps": cb["steps"], "warmup": max(0, min(args.warmup, 1)),
+        "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD_NAMES[args.config], "sample": cb["sample"],
+                   "note": "reference is JAX/Flax; jax is not installable here, so this arm times the oracle port "
+                           "of its CPU path on the host cores"},
+        "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": cb["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def gemm_replay_ms(model, M: int, iters: int = 3) -> float:
+    """CUDA-event time of exactly the GEMM launches of one training step (fwd, dgrad, wgrad of every Dense),
+    replayed back to back on scratch buffers; returns ms per step-worth of GEMMs."""
+    import torch
+    from plaincv_b200 import ops
+    L = model.layout
+    d, hp, Vp = L.d, L.hid_pad, L.V_pad
+    dev = model.flat_grad.device
+    bf = torch.bfloat16
+    x_d = torch.randn(M, d, device=dev).to(bf)
+    x_hp = torch.randn(M, hp, device=dev).to(bf)
+    y_3d = torch.randn(M, 3 * d, device=dev).to(bf)
+    y_2hp = torch.randn(M, 2 * hp, device=dev).to(bf)
+    y_V = torch.randn(M, Vp, device=dev).to(bf) * 0.01
+    o_d = torch.empty(M, d, device=dev, dtype=bf)
+    o_hp = torch.empty(M, hp, device=dev, dtype=bf)
+    layer = model.layers[0]
+    gscratch = torch.zeros_like(model.flat_grad)
+    g = lambda name: L.slot_view(gscratch, name)  # noqa: E731
+
+    def lin(x, w, y):
+        Mx, K = x.shape
+        Np = w.shape[1]
+        ops.gemm(x, w, y, Mx, Np, K, K, Np, Np, False, True, ops.PCV_EPI_BF16)
+
+    def dgrad(dy, w, dx):
+        Mx, Np = dy.shape
+        K = w.shape[0]
+        ops.gemm(dy, w, dx, Mx, K, Np, Np, Np, K, False, False, ops.PCV_EPI_BF16)
+
+    def one_step():
+        for _ in range(model.cfg.n_layers):
+            lin(x_d, layer.w_qkv, y_3d)
+            lin(x_d, layer.w_out, o_d)
+            lin(x_d, layer.w_gu, y_2hp)
+            lin(x_hp, layer.w_down, o_d)
+            dgrad(x_d, layer.w_down, o_hp)
+            ops.linear_wgrad(x_hp, x_d, g("layers_0.w_down"))
+            dgrad(y_2hp, layer.w_gu, o_d)
+            ops.linear_wgrad(x_d, y_2hp, g("layers_0.w_gu"))
+            dgrad(x_d, layer.w_out, o_d)
+            ops.linear_wgrad(x_d, x_d, g("layers_0.w_out"))
+            dgrad(y_3d, layer.w_qkv, o_d)
+            ops.linear_wgrad(x_d, y_3d, g("layers_0.w_qkv"))
+        lin(x_d, model.head.w_lm, y_V)
+        dgrad(y_V, model.head.w_lm, o_d)
+        ops.linear_wgrad(x_d, y_V, g("w_lm"))
+
+    one_step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        one_step()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def gpu_main(args) -> None:
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device; plaincv_b200 has no CPU fallback "
+                           "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from plaincv_b200 import _lib
+    from plaincv_b200.engine import Engine
+    from plaincv_b200.model import construct_model
+    from oracle import lm_oracle as O  # synthetic batch generator only (host data, not compute)
+
+    c = CONFIGS[args.config]
+    B, T, V = c["micro_batch"], c["seq_len"], c["vocab_size"]
+    model, mcfg = construct_model(yaml_like_cfg(c), device=dev)
+    eng = Engine(model, seq_len=T, use_doc_mask=c["doc"])
+    lib = _lib.load()
+    tokens_per_step = B * T * world
+
+    batch = O.synthetic_batch(B, T, V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
+    inputs_h, labels_h, ds_h = eng_prepare(eng, batch)
+    inputs_d, labels_d = inputs_h.to(dev), labels_h.to(dev)
+    ds_d = None if ds_h is None else ds_h.to(dev)
+
+    def step_resident():
+        model.flat_grad.zero_()
+        model.sync_compute_weights()
+        eng._arm_hooks(True)
+        loss, acc = model.loss_and_acc(inputs_d, labels_d, doc_start=ds_d, unit_grad=True)
+        loss.backward()
+        if world > 1:
+            eng.reducer.finish()
+        eng._arm_hooks(False)
+        return loss
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        l0 = lib.pcv_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        launches = lib.pcv_launch_count() - l0
+        clocks = sampler.stop()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / steps, launches, clocks, wall
+
+    ms_step, launches, clocks, _ = timed(step_resident, args.steps, args.warmup)
+
+    # end to end: host batch -> Engine.compute_grads -> loss read back, every step
+    def step_e2e():
+        model.sync_compute_weights()
+        loss, acc = eng.compute_grads(batch)
+        return float(loss)  # device -> host read of the step's result
+
+    ms_e2e, _, _, _ = timed(step_e2e, args.steps, min(args.warmup, 2) if args.warmup else 0)
+    loss_val = step_e2e()
+
+    line = None
+    if rank == 0:
+        peaks = load_peaks()
+        fpt = flops_per_token(c)
+        tok_s = tokens_per_step / (ms_step / 1e3)
+        tok_s_e2e = tokens_per_step / (ms_e2e / 1e3)
+        gemm_ms = gemm_replay_ms(model, B * T)
+        gemm_tf = gemm_flops_per_token(c) * B * T / (gemm_ms / 1e3) / 1e12
+        line = {
+            "metric": "train tokens/s fwd+bwd", "value": tok_s, "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD_NAMES[args.config], "global_batch": B * world, "seq_len": T,
+                       "micro_batch_per_gpu": B, "parallelism": f"dp{world}", "params": model.count_params()[0],
+                       "flop_per_token": fpt, "weights": "random-init (seed 100), fp32 masters + bf16 compute copies",
+                       "l2": "working set per step (0.8 GB bf16 weights + ~13 GB activations at c3) >> 126 MB L2",
+                       "step": "zero grads + bf16 weight refresh + fwd + bwd + (N>1) bucketed fp32 all-reduce"},
+            "mfu": {"of_burst_peak": tok_s * fpt / (world * peaks["bf16_tflops"] * 1e12),
+                    "of_sustained_peak": tok_s * fpt / (world * peaks["bf16_tflops_sustained"] * 1e12),
+                    "peaks": peaks["_source"]},
+            "e2e": {"value": tok_s_e2e, "unit": "tokens/s", "h2d_bytes_per_step": int(2 * B * T * 4 +
+                                                                                       (B * T * 4 if c["doc"] else 0)),
+                    "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e},
+            "gpu_launches": int(launches), "clocks": clocks, "loss": loss_val,
+            "roofline": {"kernel": "pcv::gemm_bf16_kernel (all Dense fwd/dgrad/wgrad launches of one step)",
+                         "bound": "tensor", "achieved": gemm_tf, "peak": peaks["bf16_tflops_sustained"] / 1.0,
+                         "unit": "TFLOP/s", "frac": gemm_tf / peaks["bf16_tflops_sustained"], "traffic": None,
+                         "peak_source": peaks["_source"] + " bf16_tflops_sustained",
+                         "gemm_ms_per_step": gemm_ms, "gemm_share_of_step": gemm_ms / ms_step},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cb = run_cpu_arm(args.config, 2, 1, max_seconds=90.0)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def eng_prepare(eng, batch):
+    from plaincv_b200.batch import prepare_batch
+    inputs, labels, ds = prepare_batch(batch, eng.seq_len, eng.use_doc_mask)
+    return inputs.contiguous().pin_memory(), labels.contiguous().pin_memory(), (None if ds is None else ds.pin_memory())
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_main(args)
+    else:
+        gpu_main(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -343,7 +343,7 @@ class HeadLossFn(torch.autograd.Function):
         res_f, hf, rstd = rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
         logits = linear_fwd(hf, head.w_lm)
         M = logits.shape[0]
-        need_grad = torch.is_grad_enabled() and res.requires_grad
+        need_grad = bool(ctx.needs_input_grad[0])
         out2, dlogits = softmax_ce(logits, labels, head.vocab, loss_scale / M, need_grad)
         if need_grad:
             ctx.save_for_backward(res_f, rstd, hf, dlogits)
