@@ -46,7 +46,7 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
 }
 __device__ __forceinline__ uint4 ld_global_nc_v4(const void* p) {
   uint4 v;
-  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  asm("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -70,17 +70,30 @@ __device__ __forceinline__ uint4 rope_chunk(uint4 raw, float4 cs0, float4 cs1, f
 __device__ __forceinline__ void load_rope_tile(uint32_t smem_tile, const __nv_bfloat16* __restrict__ gcol, int ld,
                                                long grow0, int t0, int T, const float* __restrict__ cos_sin, int ltid) {
   const int c = ltid & 7, rsub = ltid >> 3;
+  // all 8 row loads are issued before any is consumed (one memory round trip per tile, not eight)
+  uint4 raw[8];
 #pragma unroll
   for (int it = 0; it < 8; ++it) {
     const int r = it * 16 + rsub;
-    const int t = t0 + r;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (t < T) {
-      const uint4 raw = ld_global_nc_v4(gcol + (grow0 + r) * ld + c * 8);
-      const float4* cs = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(t) * 32 + c * 4) * 2);
-      v = rope_chunk(raw, __ldg(cs), __ldg(cs + 1), 1.f);
+    raw[it] = (t0 + r < T) ? ld_global_nc_v4(gcol + (grow0 + r) * ld + c * 8) : make_uint4(0, 0, 0, 0);
+  }
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    float4 cs[4][2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int t = min(t0 + (half * 4 + k) * 16 + rsub, T - 1);
+      const float4* p = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(t) * 32 + c * 4) * 2);
+      cs[k][0] = __ldg(p);
+      cs[k][1] = __ldg(p + 1);
     }
-    st_shared_v4(smem_tile + r * 128 + ((c ^ (r & 7)) << 4), v);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int it = half * 4 + k;
+      const int r = it * 16 + rsub;
+      const uint4 v = rope_chunk(raw[it], cs[k][0], cs[k][1], 1.f);
+      st_shared_v4(smem_tile + r * 128 + ((c ^ (r & 7)) << 4), v);
+    }
   }
 }
 

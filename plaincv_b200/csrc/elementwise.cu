@@ -139,9 +139,11 @@ rmsnorm_residual_fwd_kernel(const __nv_bfloat16* __restrict__ res_in, const __nv
   }
 }
 
-// Backward: persistent over rows so that each block reduces its dscale partial once.
+// Backward: persistent over rows so that each block reduces its dscale partial once.  Register diet (bf16 inputs stay
+// packed, the scale is re-read from L1) so that two 256-thread blocks fit per SM and every load of a row — dy, x and the
+// incoming residual gradient — is in flight before the first use.
 template <int VPL>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 rmsnorm_residual_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dres_out,
                             const __nv_bfloat16* __restrict__ xres, const float* __restrict__ scale,
                             const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dres_in,
@@ -150,38 +152,40 @@ rmsnorm_residual_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfl
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int vpr = d / 8;
   float ds[VPL][8];
-  float sc[VPL][8];
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    const int v = lane + 32 * i;
+  for (int i = 0; i < VPL; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      ds[i][j] = 0.f;
-      sc[i][j] = (v < vpr) ? __ldg(scale + v * 8 + j) : 0.f;
-    }
-  }
+    for (int j = 0; j < 8; ++j) ds[i][j] = 0.f;
   const float inv_d = 1.f / static_cast<float>(d);
   for (int row = blockIdx.x * nwarps + warp; row < M; row += gridDim.x * nwarps) {
     const long base = static_cast<long>(row) * d;
+    bf16x8 rdy[VPL], rx[VPL], rres[VPL];
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int v = lane + 32 * i;
+      if (v < vpr) {
+        rdy[i].raw = *reinterpret_cast<const uint4*>(dy + base + v * 8);
+        rx[i].raw = *reinterpret_cast<const uint4*>(xres + base + v * 8);
+        if (dres_out != nullptr) rres[i].raw = *reinterpret_cast<const uint4*>(dres_out + base + v * 8);
+      }
+    }
     const float rstd = rstd_in[row];
-    float g[VPL][8], xh[VPL][8];
     float dot = 0.f;
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
       const int v = lane + 32 * i;
       if (v < vpr) {
-        bf16x8 a, b;
-        a.raw = *reinterpret_cast<const uint4*>(dy + base + v * 8);
-        b.raw = *reinterpret_cast<const uint4*>(xres + base + v * 8);
-        float t[8];
-        a.unpack(t);
-        b.unpack(xh[i]);
+        float t[8], xh[8];
+        rdy[i].unpack(t);
+        rx[i].unpack(xh);
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + v * 8));
+        const float4 s1 = __ldg(reinterpret_cast<const float4*>(scale + v * 8 + 4));
+        const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          xh[i][j] *= rstd;
-          ds[i][j] += t[j] * xh[i][j];
-          g[i][j] = t[j] * sc[i][j];
-          dot += g[i][j] * xh[i][j];
+          xh[j] *= rstd;
+          ds[i][j] += t[j] * xh[j];
+          dot += t[j] * sc[j] * xh[j];
         }
       }
     }
@@ -190,16 +194,19 @@ rmsnorm_residual_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfl
     for (int i = 0; i < VPL; ++i) {
       const int v = lane + 32 * i;
       if (v < vpr) {
-        float o[8];
+        float t[8], xh[8], o[8];
+        rdy[i].unpack(t);
+        rx[i].unpack(xh);
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + v * 8));
+        const float4 s1 = __ldg(reinterpret_cast<const float4*>(scale + v * 8 + 4));
+        const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (t[j] * sc[j] - xh[j] * rstd * dot);
         if (dres_out != nullptr) {
-          bf16x8 r;
-          r.raw = *reinterpret_cast<const uint4*>(dres_out + base + v * 8);
-          float t[8];
-          r.unpack(t);
+          float r[8];
+          rres[i].unpack(r);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] += t[j];
+          for (int j = 0; j < 8; ++j) o[j] += r[j];
         }
         bf16x8 w;
         w.pack(o);
@@ -367,7 +374,7 @@ template <int VPL>
 static int launch_rms_bwd(const void* dy, const void* dres_out, const void* res_out, const float* scale,
                           const float* rstd, void* dres_in, float* dscale, int M, int d, cudaStream_t st) {
   const int threads = 256, nwarps = threads / 32;
-  int grid = num_sms() * 4;
+  int grid = num_sms() * 2;
   const int max_grid = (M + nwarps - 1) / nwarps;
   if (grid > max_grid) grid = max_grid;
   const size_t smem = static_cast<size_t>(nwarps) * d * sizeof(float);

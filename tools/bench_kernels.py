@@ -1,0 +1,107 @@
+#!/usr/bin/env python
+"""Per-kernel CUDA-event timings at the 420M (C3) shapes; prints achieved TFLOP/s or GB/s.  GPU box only.
+usage: python tools/bench_kernels.py [T] [which]   (which: all | attn | ew | gemm)"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from plaincv_b200 import ops  # noqa: E402
+
+dev = "cuda"
+bf = torch.bfloat16
+B, T, NH, d, hp, Vp = 8, 2048, 16, 1024, 2736, 50280
+if len(sys.argv) > 1:
+    T = int(sys.argv[1])
+    B = 16384 // T
+which = sys.argv[2] if len(sys.argv) > 2 else "all"
+M = B * T
+flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+res = {}
+
+
+def timeit(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / iters
+
+
+if which in ("all", "attn"):
+    qkv = torch.randn(M, 3 * d, device=dev).to(bf)
+    cos_sin = ops.rope_table(64, T, 500000.0, dev)
+    out, lse = ops.attn_fwd(qkv, cos_sin, None, B, T, NH)
+    dout = torch.randn(M, d, device=dev).to(bf)
+    fl_fwd = 4.0 * B * NH * T * T * 64 / 2
+    ms = timeit(lambda: ops.attn_fwd(qkv, cos_sin, None, B, T, NH))
+    res["attn_fwd"] = (ms, fl_fwd / ms / 1e9, "TFLOP/s (causal-half flops)")
+    ms = timeit(lambda: ops.attn_bwd(qkv, cos_sin, None, out, dout, lse, B, T, NH))
+    res["attn_bwd"] = (ms, 2.5 * fl_fwd / ms / 1e9, "TFLOP/s (5 GEMMs, causal-half)")
+    ds = torch.zeros(B, T, dtype=torch.int32)
+    g = torch.Generator().manual_seed(0)
+    for b in range(B):
+        t = 0
+        while t < T:
+            n = int(max(1, min(T - t, torch.empty(1).exponential_(1 / 512.0, generator=g).item())))
+            ds[b, t:t + n] = t
+            t += n
+    ds = ds.to(dev).view(-1)
+    ms = timeit(lambda: ops.attn_fwd(qkv, cos_sin, ds, B, T, NH))
+    res["attn_fwd_doc512"] = (ms, 0, "")
+    ms = timeit(lambda: ops.attn_bwd(qkv, cos_sin, ds, out, dout, lse, B, T, NH))
+    res["attn_bwd_doc512"] = (ms, 0, "")
+
+if which in ("all", "ew"):
+    x = torch.randn(M, d, device=dev).to(bf)
+    dl = torch.randn(M, d, device=dev).to(bf)
+    scale = torch.ones(d, device=dev)
+    dscale = torch.zeros(d, device=dev)
+    ro, y, rstd = ops.rmsnorm_residual_fwd(x, dl, scale, 1e-6)
+    ms = timeit(lambda: ops.rmsnorm_residual_fwd(x, dl, scale, 1e-6))
+    res["rmsnorm_res_fwd"] = (ms, 4 * M * d * 2 / ms / 1e6, "GB/s")
+    ms = timeit(lambda: ops.rmsnorm_residual_bwd(x, dl, ro, scale, rstd, dscale))
+    res["rmsnorm_res_bwd"] = (ms, 4 * M * d * 2 / ms / 1e6, "GB/s")
+    gu = torch.randn(M, 2 * hp, device=dev).to(bf)
+    dh = torch.randn(M, hp, device=dev).to(bf)
+    ms = timeit(lambda: ops.swiglu_fwd(gu))
+    res["swiglu_fwd"] = (ms, 3 * M * hp * 2 / ms / 1e6, "GB/s")
+    ms = timeit(lambda: ops.swiglu_bwd(gu, dh))
+    res["swiglu_bwd"] = (ms, 5 * M * hp * 2 / ms / 1e6, "GB/s")
+    logits = (torch.randn(M, Vp, device=dev) * 2).to(bf)
+    labels = torch.randint(0, Vp, (M,), device=dev, dtype=torch.int32)
+    ms = timeit(lambda: ops.softmax_ce(logits, labels, Vp, 1.0 / M, True))
+    res["softmax_ce(+grad)"] = (ms, 2 * M * Vp * 2 / ms / 1e6, "GB/s")
+    del logits
+
+if which in ("all", "gemm"):
+    def gemm_set(name, K, N):
+        xx = torch.randn(M, K, device=dev).to(bf)
+        w = (torch.randn(K, N, device=dev) * 0.02).to(bf)
+        dy = torch.randn(M, N, device=dev).to(bf)
+        dw = torch.zeros(K, N, device=dev)
+        fl = 2.0 * M * K * N
+        ms = timeit(lambda: ops.linear_fwd(xx, w))
+        res[f"gemm_fwd_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: ops.linear_dgrad(dy, w))
+        res[f"gemm_dgrad_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: ops.linear_wgrad(xx, dy, dw))
+        res[f"gemm_wgrad_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
+
+    gemm_set("qkv", d, 3 * d)
+    gemm_set("out", d, d)
+    gemm_set("gu", d, 2 * hp)
+    gemm_set("down", hp, d)
+    gemm_set("lm", d, Vp)
+
+for k, (ms, v, u) in res.items():
+    print(f"{k:24s} {ms*1e3:9.1f} us   {v:9.1f} {u}")
