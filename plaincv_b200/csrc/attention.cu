@@ -31,6 +31,14 @@
 
 namespace pcv {
 
+#ifdef PCV_TRACE
+// Debug-only timeline (clock64 at phase boundaries of CTA (0,0,0)); compiled in with -DPCV_TRACE, never in the product build.
+__device__ long long g_trace[8192];
+#define TRACE(slot, idx) do { if (trace_on && (idx) < 1024) g_trace[(slot) * 1024 + (idx)] = clock64(); } while (0)
+#else
+#define TRACE(slot, idx) do { } while (0)
+#endif
+
 constexpr int kAttnThreads = 416;
 constexpr int kTileBytes = 128 * 128;  // 128 rows x 64 bf16
 constexpr float kLog2e = 1.4426950408889634f;
@@ -97,6 +105,56 @@ __device__ __forceinline__ void load_rope_tile(uint32_t smem_tile, const __nv_bf
   }
 }
 
+// ---- softmax chunk helpers (32 score columns held by one thread).  MASK variants take the valid column window
+// [lo, hi] relative to the chunk start; the unmasked variants are branch- and select-free.
+template <bool MASK>
+__device__ __forceinline__ float chunk_rowmax(const uint32_t* sr, int lo, int hi, float rmax) {
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    float v = __uint_as_float(sr[k]);
+    if (MASK) v = (k >= lo && k <= hi) ? v : -INFINITY;
+    rmax = fmaxf(rmax, v);
+  }
+  return rmax;
+}
+// p = exp2(s*c2 - mb) -> packed bf16 pairs; returns the fp32 row-sum contribution
+template <bool MASK>
+__device__ __forceinline__ float chunk_exp_pack(const uint32_t* sr, float c2, float mb, int lo, int hi, uint32_t* packed) {
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 32; k += 2) {
+    float e0 = ex2f(fmaf(__uint_as_float(sr[k]), c2, -mb));
+    float e1 = ex2f(fmaf(__uint_as_float(sr[k + 1]), c2, -mb));
+    if (MASK) {
+      e0 = (k >= lo && k <= hi) ? e0 : 0.f;
+      e1 = (k + 1 >= lo && k + 1 <= hi) ? e1 : 0.f;
+    }
+    s0 += e0;
+    s1 += e1;
+    packed[k >> 1] = pack_bf16x2(e0, e1);
+  }
+  return s0 + s1;
+}
+
+// backward: p = exp2(s*c2 - lse2), ds = p * (dp*scale - delta*scale), both packed to bf16 pairs
+template <bool MASK>
+__device__ __forceinline__ void chunk_p_ds(const uint32_t* sr, const uint32_t* pr, float c2, float lse2, float dlt_s,
+                                           int lo, int hi, uint32_t* pk_p, uint32_t* pk_ds) {
+#pragma unroll
+  for (int k = 0; k < 32; k += 2) {
+    float e0 = ex2f(fmaf(__uint_as_float(sr[k]), c2, -lse2));
+    float e1 = ex2f(fmaf(__uint_as_float(sr[k + 1]), c2, -lse2));
+    if (MASK) {
+      e0 = (k >= lo && k <= hi) ? e0 : 0.f;
+      e1 = (k + 1 >= lo && k + 1 <= hi) ? e1 : 0.f;
+    }
+    const float g0 = e0 * fmaf(__uint_as_float(pr[k]), kSoftmaxScale, -dlt_s);
+    const float g1 = e1 * fmaf(__uint_as_float(pr[k + 1]), kSoftmaxScale, -dlt_s);
+    pk_p[k >> 1] = pack_bf16x2(e0, e1);
+    pk_ds[k >> 1] = pack_bf16x2(g0, g1);
+  }
+}
+
 // ================================================================================================ forward
 struct AttnFwdSmem {
   static constexpr int kQ = 0;                          // 2 tiles
@@ -127,6 +185,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef PCV_TRACE
+  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 384);
+#endif
   const int n_qblk = gridDim.x;
   const int qblk = n_qblk - 1 - blockIdx.x;  // heaviest (latest) query blocks first
   const int h = blockIdx.y, b = blockIdx.z;
@@ -235,20 +296,26 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
         const int last_w = active(1, j) ? 1 : 0;
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
-          if (active(w, j)) {
-            const int i = j - jmin[w];
-            mbar_wait(bPfull(w), i & 1);
-            mbar_wait(bVfull(slot), use_par);
-            tc_fence_after();
-            issue_PV(w, slot, i & 1);
+          const bool act = active(w, j);
+          const bool nxt = (j + 1 <= jhi) && active(w, j + 1);
+          const int i = j - jmin[w];
+          if (act) {
+            TRACE(4 + w, i * 2 + 0);
+            mbar_wait(bPfull(w), i & 1);  // P_w(j) is in shared memory and S_w has been consumed
+            TRACE(4 + w, i * 2 + 1);
           }
-          if (w == last_w) tc_commit(bKVempty(slot));
-          if (j + 1 <= jhi && active(w, j + 1)) {
+          if (nxt) {  // next S first: it is what the softmax warpgroup waits for
             const int slot1 = (idx + 1) % 3;
             mbar_wait(bKready(slot1), ((idx + 1) / 3) & 1);
             tc_fence_after();
             issue_S(w, slot1);
           }
+          if (act) {
+            mbar_wait(bVfull(slot), use_par);
+            tc_fence_after();
+            issue_PV(w, slot, i & 1);
+          }
+          if (w == last_w) tc_commit(bKVempty(slot));
         }
       }
     }
@@ -269,70 +336,75 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
       float acc[64];
 #pragma unroll
       for (int k = 0; k < 64; ++k) acc[k] = 0.f;
-      float m_run = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
+      float m_seen = -INFINITY, ref = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
       const int n_it = jmax[w] - jmin[w] + 1;
       for (int i = 0; i < n_it; ++i) {
         const int j = jmin[w] + i;
+        TRACE(w * 2 + 0, i * 4 + 0);
         mbar_wait(bSfull(w), i & 1);
         tc_fence_after();
+        TRACE(w * 2 + 0, i * 4 + 1);
         const bool need_mask = (j * 128 + 127 > q0 + 128 * w) || (j * 128 < ds_hi);
         const int key0 = j * 128;
-        // ---- pass 1: row max
-        float rmax = -INFINITY;
+        const int hi0 = t - key0, lo0 = ds_t - key0;  // valid key window relative to the tile start
+        // Reference for the exponent.  Exact tiles (the first one, and masked ones) take the row max in a first pass
+        // over S; every other tile re-uses the running max of the tiles before it ("lazy" reference: the result is
+        // identical after normalisation, and one TMEM pass over S is saved).  A lazy tile whose scores exceed the
+        // reference by more than 2^60 (or whose reference is still -inf) is redone exactly.
+        bool exact = (i == 0) || need_mask;
+        float ref_new = m_seen;
+        if (exact) {
+          float rmax = -INFINITY;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t sr[32];
-          tmem_ld_32x32b_x32(tS + c * 32, sr);
-          tmem_ld_wait();
-          if (need_mask) {
-#pragma unroll
-            for (int k = 0; k < 32; ++k) {
-              const int key = key0 + c * 32 + k;
-              if (key <= t && key >= ds_t) rmax = fmaxf(rmax, __uint_as_float(sr[k]));
-            }
-          } else {
-#pragma unroll
-            for (int k = 0; k < 32; ++k) rmax = fmaxf(rmax, __uint_as_float(sr[k]));
+          for (int c = 0; c < 4; ++c) {
+            uint32_t sr[32];
+            tmem_ld_32x32b_x32(tS + c * 32, sr);
+            tmem_ld_wait();
+            rmax = need_mask ? chunk_rowmax<true>(sr, lo0 - c * 32, hi0 - c * 32, rmax)
+                             : chunk_rowmax<false>(sr, 0, 0, rmax);
           }
+          ref_new = fmaxf(m_seen, rmax);
         }
-        const float m_new = fmaxf(m_run, rmax);
-        const float m_eff = (m_new == -INFINITY) ? 0.f : m_new;
-        const float alpha = ex2f((m_run - m_eff) * c2);  // m_run = -inf -> 0
-        const float mb = m_eff * c2;
-        // ---- pass 2: P = exp2(S*c2 - m*c2) -> bf16 -> shared memory (K-major, swizzled); row sum in fp32
-        float psum = 0.f;
+        TRACE(w * 2 + 0, i * 4 + 2);
+        float psum, tile_max, alpha;
+        while (true) {
+          const float ref_eff = (ref_new == -INFINITY) ? 0.f : ref_new;
+          alpha = ex2f((ref - ref_eff) * c2);  // ref = -inf -> 0
+          const float mb = ref_eff * c2;
+          psum = 0.f;
+          tile_max = -INFINITY;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t sr[32];
-          tmem_ld_32x32b_x32(tS + c * 32, sr);
-          tmem_ld_wait();
-          float p[32];
-#pragma unroll
-          for (int k = 0; k < 32; ++k) {
-            float e = ex2f(fmaf(__uint_as_float(sr[k]), c2, -mb));
+          for (int c = 0; c < 4; ++c) {
+            uint32_t sr[32];
+            tmem_ld_32x32b_x32(tS + c * 32, sr);
+            tmem_ld_wait();
+            uint32_t pk[16];
             if (need_mask) {
-              const int key = key0 + c * 32 + k;
-              if (!(key <= t && key >= ds_t)) e = 0.f;
+              psum += chunk_exp_pack<true>(sr, c2, mb, lo0 - c * 32, hi0 - c * 32, pk);
+            } else {
+              psum += chunk_exp_pack<false>(sr, c2, mb, 0, 0, pk);
+              if (!exact) tile_max = chunk_rowmax<false>(sr, 0, 0, tile_max);
             }
-            p[k] = e;
-            psum += e;
-          }
+            const uint32_t prow = sPw + (c >> 1) * kTileBytes + r * 128;
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            uint4 o;
-            o.x = pack_bf16x2(p[v * 8 + 0], p[v * 8 + 1]);
-            o.y = pack_bf16x2(p[v * 8 + 2], p[v * 8 + 3]);
-            o.z = pack_bf16x2(p[v * 8 + 4], p[v * 8 + 5]);
-            o.w = pack_bf16x2(p[v * 8 + 6], p[v * 8 + 7]);
-            const int chunk = c * 4 + v;  // 16-byte chunk index within the 256-byte P row
-            st_shared_v4(sPw + (chunk >> 3) * kTileBytes + r * 128 + (((chunk & 7) ^ (r & 7)) << 4), o);
+            for (int v = 0; v < 4; ++v) {
+              const int cc = (c & 1) * 4 + v;  // 16-byte chunk index within the 128-byte half row
+              st_shared_v4(prow + ((cc ^ (r & 7)) << 4), make_uint4(pk[v * 4], pk[v * 4 + 1], pk[v * 4 + 2], pk[v * 4 + 3]));
+            }
           }
+          if (exact) break;
+          const bool bad = !((tile_max - ref_new) * c2 <= 60.f);  // also true for ref = -inf / NaN
+          if (!__any_sync(0xffffffffu, bad)) break;
+          ref_new = fmaxf(m_seen, tile_max);
+          exact = true;
         }
+        m_seen = exact ? ref_new : fmaxf(m_seen, tile_max);
+        ref = ref_new;
         l_run = l_run * alpha + psum;
-        m_run = m_new;
         tc_fence_before();
         fence_proxy_async_smem();
         mbar_arrive(bPfull(w));
+        TRACE(w * 2 + 0, i * 4 + 3);
         // ---- fold the previous tile's P.V (already complete: its MMAs precede S_i in the tensor pipe)
         if (i > 0) {
           const int ob = (i - 1) & 1;
@@ -374,7 +446,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
             o.w = pack_bf16x2(acc[v * 8 + 6], acc[v * 8 + 7]);
             *reinterpret_cast<uint4*>(orow + v * 8) = o;
           }
-          lse[(static_cast<long>(b) * NH + h) * T + t] = m_run * kSoftmaxScale + logf(l_run);
+          lse[(static_cast<long>(b) * NH + h) * T + t] = ref * kSoftmaxScale + logf(l_run);
         }
       }
     }
@@ -423,13 +495,14 @@ struct AttnBwdSmem {
   static constexpr int kdO = kQ + 2 * kTileBytes;   // 2 stages
   static constexpr int kP = kdO + 2 * kTileBytes;   // 128 x 128 bf16
   static constexpr int kdS = kP + 2 * kTileBytes;   // 128 x 128 bf16
-  static constexpr int kBar = kdS + 2 * kTileBytes;
+  static constexpr int kdQ = kdS + 2 * kTileBytes;  // fp32 staging of dQ: 2 halves x (128 rows x 32 columns)
+  static constexpr int kBar = kdQ + 2 * kTileBytes;
   static constexpr int kBytes = kBar + 256 + 1024;
 };
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                const __nv_bfloat16* __restrict__ qkv, const float* __restrict__ cos_sin,
+                const __grid_constant__ CUtensorMap tm_dq, const __nv_bfloat16* __restrict__ qkv, const float* __restrict__ cos_sin,
                 const int32_t* __restrict__ doc_start, const float* __restrict__ lse, const float* __restrict__ delta,
                 float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
@@ -451,6 +524,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef PCV_TRACE
+  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 384);
+#endif
   const int j = blockIdx.x;  // key tile
   const int h = blockIdx.y, b = blockIdx.z;
   const int d = NH * 64, ld = 3 * d;
@@ -475,6 +551,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   if (warp == 12 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
+    tma_prefetch_desc(&tm_dq);
     mbar_init(bKready, 128);
     mbar_init(bVfull, 1);
     for (int s = 0; s < 2; ++s) {
@@ -550,30 +627,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
       for (int it = 0; it < n_it; ++it) {
         const int stage = it & 1;
-        mbar_wait(bPdSfull, it & 1);
-        mbar_wait(bdQempty, (it & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
+        const uint32_t sPb = sP, sdSb = sdS;
+        TRACE(4, it * 2 + 0);
+        mbar_wait(bPdSfull, it & 1);  // P/dS(it) are in shared memory; S/dP in TMEM have been consumed
         tc_fence_after();
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {  // contraction over the 128 query rows, 16 per step
-          // A = P^T (MN-major view of P[q][key]: two 64-key atoms 16 KB apart); B = dO (MN-major)
-          const uint64_t da = umma_smem_desc(sP + k * 2048, kTileBytes, 1024);
-          const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint64_t da = umma_smem_desc(sdS + k * 2048, kTileBytes, 1024);
-          const uint64_t db = umma_smem_desc(sQ + stage * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tdK, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {  // contraction over the 128 keys
-          const uint64_t da = umma_smem_desc(sdS + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
-          const uint64_t db = umma_smem_desc(sK + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tdQ, da, db, idesc_dq, k > 0 ? 1u : 0u);
-        }
-        tc_commit(bdQfull);
-        tc_commit(bStageEmpty(stage));
+        TRACE(4, it * 2 + 1);
+        // next tile's S and dP first: they are what the compute warps wait for
         if (it + 1 < n_it) {
           const int s1 = (it + 1) & 1;
           mbar_wait(bQready(s1), ((it + 1) >> 1) & 1);
@@ -581,6 +640,29 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           tc_fence_after();
           issue_SdP(s1);
         }
+        mbar_wait(bdQempty, (it & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // contraction over the 128 query rows, 16 per step
+          // A = P^T (MN-major view of P[q][key]: two 64-key atoms 16 KB apart); B = dO (MN-major)
+          const uint64_t da = umma_smem_desc(sPb + k * 2048, kTileBytes, 1024);
+          const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint64_t da = umma_smem_desc(sdSb + k * 2048, kTileBytes, 1024);
+          const uint64_t db = umma_smem_desc(sQ + stage * kTileBytes + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tdK, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // contraction over the 128 keys
+          const uint64_t da = umma_smem_desc(sdSb + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sK + k * 2048, kTileBytes, 1024);
+          umma_bf16_ss(tdQ, da, db, idesc_dq, k > 0 ? 1u : 0u);
+        }
+        tc_commit(bdQfull);
+        tc_commit(bStageEmpty(stage));
       }
       tc_commit(bAccFull);
     }
@@ -591,88 +673,82 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const int half = tid >> 7;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     constexpr float c2 = kSoftmaxScale * kLog2e;
+    // dQ of query tile (i_lo + itp): TMEM -> fp32 staging tile in shared memory -> one TMA reduce-add per 32-column
+    // half into dq_acc (fp32, L2-side add).
+    auto dq_readout = [&](int itp) {
+      mbar_wait(bdQfull, itp & 1);
+      tc_fence_after();
+      uint32_t qr[32];
+      tmem_ld_32x32b_x32(tdQ + lane_off + half * 32, qr);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(bdQempty);
+      if (tid == 0) tma_store_wait_read<0>();  // earlier reduce-adds have finished reading their staging tiles
+      named_bar_sync(1, 256);
+      const uint32_t stage_base = sbase + AttnBwdSmem::kdQ;
+      const uint32_t srow = stage_base + half * kTileBytes + r * 128;
+#pragma unroll
+      for (int v = 0; v < 8; ++v)
+        st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(qr[v * 4], qr[v * 4 + 1], qr[v * 4 + 2], qr[v * 4 + 3]));
+      fence_proxy_async_smem();
+      named_bar_sync(1, 256);
+      if (tid == 0) {
+        const int row0 = static_cast<int>(seq_row0) + (i_lo + itp) * 128;
+        tma_reduce_add_2d(&tm_dq, stage_base, h * 64, row0);
+        tma_reduce_add_2d(&tm_dq, stage_base + kTileBytes, h * 64 + 32, row0);
+        tma_store_commit();
+      }
+    };
     for (int it = 0; it < n_it; ++it) {
       const int i = i_lo + it;
       const int t = i * 128 + r;
       const long stat_idx = (static_cast<long>(b) * NH + h) * T + min(t, T - 1);
       const float lse2 = lse[stat_idx] * kLog2e;
-      const float dlt = delta[stat_idx];
+      const float dlt_s = delta[stat_idx] * kSoftmaxScale;
       const int ds_t = doc_start ? doc_start[seq_row0 + min(t, T - 1)] : 0;
-      const bool need_mask = (key0 + 127 > i * 128) || (doc_start != nullptr);
+      const int ds_hi_of_tile = doc_start ? doc_start[seq_row0 + min(i * 128 + 127, T - 1)] : 0;
+      const bool need_mask = (key0 + 127 > i * 128) || (key0 < ds_hi_of_tile);
+      TRACE(half, it * 4 + 0);
       mbar_wait(bSdPfull, it & 1);
       tc_fence_after();
-      if (it > 0) {
-        // dQ of the previous query tile (its MMAs precede S/dP of this tile in the tensor pipe)
-        mbar_wait(bdQfull, (it - 1) & 1);
-        tc_fence_after();
-        uint32_t qr[32];
-        tmem_ld_32x32b_x32(tdQ + lane_off + half * 32, qr);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(bdQempty);
-        const int tp = (i - 1) * 128 + r;
-        if (tp < T) {
-          float* dst = dq_acc + (seq_row0 + tp) * d + h * 64 + half * 32;
+      TRACE(half, it * 4 + 1);
+      // the math for this thread's 64 columns stays in registers ...
+      uint32_t pk_p[2][16], pk_ds[2][16];
 #pragma unroll
-          for (int v = 0; v < 8; ++v)
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + v * 4), "f"(__uint_as_float(qr[v * 4 + 0])),
-                         "f"(__uint_as_float(qr[v * 4 + 1])), "f"(__uint_as_float(qr[v * 4 + 2])),
-                         "f"(__uint_as_float(qr[v * 4 + 3]))
-                         : "memory");
-        }
-      }
-#pragma unroll 1
       for (int c = 0; c < 2; ++c) {
         const int col0 = half * 64 + c * 32;
         uint32_t sr[32], pr[32];
         tmem_ld_32x32b_x32(tS + lane_off + col0, sr);
         tmem_ld_32x32b_x32(tdP + lane_off + col0, pr);
         tmem_ld_wait();
-        float p[32], ds[32];
+        if (need_mask) chunk_p_ds<true>(sr, pr, c2, lse2, dlt_s, ds_t - key0 - col0, t - key0 - col0, pk_p[c], pk_ds[c]);
+        else chunk_p_ds<false>(sr, pr, c2, lse2, dlt_s, 0, 0, pk_p[c], pk_ds[c]);
+      }
+      // ... until the previous tile's dV/dK/dQ MMAs (which read P and dS from shared memory) have completed
+      if (it > 0) mbar_wait(bdQfull, (it - 1) & 1);
+      {
+        const uint32_t rowoff = half * kTileBytes + r * 128;
 #pragma unroll
-        for (int k = 0; k < 32; ++k) {
-          float e = ex2f(fmaf(__uint_as_float(sr[k]), c2, -lse2));
-          if (need_mask) {
-            const int key = key0 + col0 + k;
-            if (!(key <= t && key >= ds_t)) e = 0.f;
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
+            st_shared_v4(sP + off, make_uint4(pk_p[c][v * 4], pk_p[c][v * 4 + 1], pk_p[c][v * 4 + 2], pk_p[c][v * 4 + 3]));
+            st_shared_v4(sdS + off, make_uint4(pk_ds[c][v * 4], pk_ds[c][v * 4 + 1], pk_ds[c][v * 4 + 2], pk_ds[c][v * 4 + 3]));
           }
-          p[k] = e;
-          ds[k] = e * (__uint_as_float(pr[k]) - dlt) * kSoftmaxScale;
-        }
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          uint4 o, g;
-          o.x = pack_bf16x2(p[v * 8 + 0], p[v * 8 + 1]); o.y = pack_bf16x2(p[v * 8 + 2], p[v * 8 + 3]);
-          o.z = pack_bf16x2(p[v * 8 + 4], p[v * 8 + 5]); o.w = pack_bf16x2(p[v * 8 + 6], p[v * 8 + 7]);
-          g.x = pack_bf16x2(ds[v * 8 + 0], ds[v * 8 + 1]); g.y = pack_bf16x2(ds[v * 8 + 2], ds[v * 8 + 3]);
-          g.z = pack_bf16x2(ds[v * 8 + 4], ds[v * 8 + 5]); g.w = pack_bf16x2(ds[v * 8 + 6], ds[v * 8 + 7]);
-          const int chunk = (col0 >> 3) + v;
-          const uint32_t off = (chunk >> 3) * kTileBytes + r * 128 + (((chunk & 7) ^ (r & 7)) << 4);
-          st_shared_v4(sP + off, o);
-          st_shared_v4(sdS + off, g);
-        }
       }
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(bPdSfull);
+      TRACE(half, it * 4 + 2);
+      // previous tile's dQ: its MMAs were queued behind this tile's S/dP, so this runs while the tensor pipe works
+      if (it > 0) dq_readout(it - 1);
+      TRACE(half, it * 4 + 3);
     }
     // ---- tail: last dQ, then dK / dV
     if (n_it > 0) {
-      mbar_wait(bdQfull, (n_it - 1) & 1);
-      tc_fence_after();
-      uint32_t qr[32];
-      tmem_ld_32x32b_x32(tdQ + lane_off + half * 32, qr);
-      tmem_ld_wait();
-      const int tp = i_hi * 128 + r;
-      if (tp < T) {
-        float* dst = dq_acc + (seq_row0 + tp) * d + h * 64 + half * 32;
-#pragma unroll
-        for (int v = 0; v < 8; ++v)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + v * 4), "f"(__uint_as_float(qr[v * 4 + 0])),
-                       "f"(__uint_as_float(qr[v * 4 + 1])), "f"(__uint_as_float(qr[v * 4 + 2])),
-                       "f"(__uint_as_float(qr[v * 4 + 3]))
-                       : "memory");
-      }
+      dq_readout(n_it - 1);
+      if (tid == 0) tma_store_wait<0>();
       mbar_wait(bAccFull, 0);
       tc_fence_after();
       // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
@@ -751,6 +827,12 @@ static int attn_check(int B, int T, int NH) {
   return PCV_OK;
 }
 
+#ifdef PCV_TRACE
+extern "C" int pcv_debug_read_trace(long long* host, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host, pcv::g_trace, sizeof(long long) * n));
+}
+#endif
+
 extern "C" int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, void* out, float* lse,
                             int B, int T, int n_heads, void* stream) {
   if (!qkv || !cos_sin || !out || !lse) return PCV_ERR_ARG;
@@ -787,6 +869,9 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   if (rc) return rc;
   rc = get_tmap_2d_bf16(&tm_do, dout, BT, d, d, 128);
   if (rc) return rc;
+  CUtensorMap tm_dq;
+  rc = get_tmap_2d_f32(&tm_dq, dq_acc, BT, d, d, 128);
+  if (rc) return rc;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::kBytes);
@@ -802,7 +887,7 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   }
   dim3 grid(T / 128, n_heads, B);
   attn_bwd_kernel<<<grid, kAttnThreads, AttnBwdSmem::kBytes, st>>>(
-      tm_qkv, tm_do, static_cast<const __nv_bfloat16*>(qkv), cos_sin, doc_start, lse, delta, dq_acc,
+      tm_qkv, tm_do, tm_dq, static_cast<const __nv_bfloat16*>(qkv), cos_sin, doc_start, lse, delta, dq_acc,
       static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
   {
     const long total = BT * (d / 8);

@@ -255,19 +255,24 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
-// 2-D bf16 row-major [rows][cols] (ld elements between rows), 128B-swizzled box {64, box_rows}.
-int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+// 2-D row-major [rows][cols] (ld elements between rows), 128B-swizzled box {128 bytes, box_rows}; bf16 or fp32.
+static int make_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                        bool f32) {
   PFN_encodeTiled enc = get_encode();
   if (!enc) return PCV_ERR_DRIVER;
-  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * 2) % 16) return PCV_ERR_ALIGN;
+  const uint64_t esz = f32 ? 4 : 2;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld * esz) % 16) return PCV_ERR_ALIGN;
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstride[1] = {ld * 2};
-  cuuint32_t box[2] = {64, box_rows};
+  cuuint64_t gstride[1] = {ld * esz};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / esz), box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                   const_cast<void*>(ptr), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? PCV_OK : PCV_ERR_TMAP;
+}
+int make_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return make_tmap_2d(out, ptr, rows, cols, ld, box_rows, false);
 }
 
 namespace {
@@ -275,8 +280,9 @@ struct TmapKey {
   const void* ptr;
   uint64_t rows, cols, ld;
   uint32_t box_rows;
+  bool f32;
   bool operator==(const TmapKey& o) const {
-    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows;
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows && f32 == o.f32;
   }
 };
 struct TmapKeyHash {
@@ -285,7 +291,7 @@ struct TmapKeyHash {
     h = h * 1000003u ^ k.rows;
     h = h * 1000003u ^ k.cols;
     h = h * 1000003u ^ k.ld;
-    h = h * 1000003u ^ k.box_rows;
+    h = h * 1000003u ^ (k.box_rows * 2u + (k.f32 ? 1u : 0u));
     return h;
   }
 };
@@ -294,8 +300,9 @@ std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmap_cache;
 }  // namespace
 
 // Descriptors depend only on (pointer, shape, box): cache them, the training step re-uses the same buffers.
-int get_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
-  TmapKey key{ptr, rows, cols, ld, box_rows};
+static int get_tmap_2d(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                       bool f32) {
+  TmapKey key{ptr, rows, cols, ld, box_rows, f32};
   {
     std::lock_guard<std::mutex> g(g_tmap_mu);
     auto it = g_tmap_cache.find(key);
@@ -304,12 +311,18 @@ int get_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t 
       return PCV_OK;
     }
   }
-  int rc = make_tmap_2d_bf16(out, ptr, rows, cols, ld, box_rows);
+  int rc = make_tmap_2d(out, ptr, rows, cols, ld, box_rows, f32);
   if (rc != PCV_OK) return rc;
   std::lock_guard<std::mutex> g(g_tmap_mu);
   if (g_tmap_cache.size() > 65536) g_tmap_cache.clear();
   g_tmap_cache.emplace(key, *out);
   return PCV_OK;
+}
+int get_tmap_2d_bf16(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return get_tmap_2d(out, ptr, rows, cols, ld, box_rows, false);
+}
+int get_tmap_2d_f32(CUtensorMap* out, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return get_tmap_2d(out, ptr, rows, cols, ld, box_rows, true);
 }
 
 int num_sms() {
