@@ -50,6 +50,23 @@ struct GemmParams {
   float alpha;
 };
 
+// Work item -> (m tile, n tile, k split).  Tiles are visited in column-major order inside groups of kGroupM tile
+// rows, so the CTAs that run concurrently share a few A tiles AND a few B tiles (L2 reuse for wide outputs such as
+// the LM head, where a plain row-major order would stream all of B for every tile row).
+constexpr int kGroupM = 16;
+__device__ __forceinline__ void decode_work(const GemmParams& p, int w, int& m_blk, int& n_blk, int& split) {
+  const int per_split = p.m_tiles * p.n_tiles;
+  split = w / per_split;
+  const int t = w - split * per_split;
+  const int per_group = kGroupM * p.n_tiles;
+  const int g = t / per_group;
+  const int first_m = g * kGroupM;
+  const int gm = min(kGroupM, p.m_tiles - first_m);
+  const int r = t - g * per_group;
+  m_blk = first_m + r % gm;
+  n_blk = r / gm;
+}
+
 template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -102,9 +119,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
-        const int n_blk = w % p.n_tiles;
-        const int m_blk = (w / p.n_tiles) % p.m_tiles;
-        const int split = w / (p.n_tiles * p.m_tiles);
+        int m_blk, n_blk, split;
+        decode_work(p, w, m_blk, n_blk, split);
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         const int m0 = m_blk * kBM, n0 = n_blk * BN;
@@ -174,8 +190,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     const int ew = warp & 3;  // TMEM lane quarter this warp may access
     int it = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++it) {
-      const int n_blk = w % p.n_tiles;
-      const int m_blk = (w / p.n_tiles) % p.m_tiles;
+      int m_blk, n_blk, split_unused;
+      decode_work(p, w, m_blk, n_blk, split_unused);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(tmem_full_bar(acc), acc_phase);

@@ -9,6 +9,12 @@
 namespace pcv {
 
 constexpr int kCeThreads = 512;
+constexpr float kLog2eF = 1.4426950408889634f;
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 struct MaxIdx {
   float m;
@@ -37,30 +43,50 @@ softmax_ce_kernel(const __nv_bfloat16* __restrict__ logits, const int32_t* __res
   // pass 1: online max / sum-exp, argmax (first max)
   float m = -FLT_MAX, s = 0.f;
   MaxIdx best{-FLT_MAX, 0x7fffffff};
-  for (int v = tid; v < nvec; v += kCeThreads) {
-    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(lrow) + v);
-    if (kCache) row_cache[v] = raw;
-    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
-    float f[8];
+  constexpr int kUnroll = 4;  // loads of one batch are all in flight before the first is consumed
+  for (int v0 = tid; v0 < nvec; v0 += kCeThreads * kUnroll) {
+    uint4 raws[kUnroll];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 t = unpack_bf16x2(w[j]);
-      f[2 * j] = t.x;
-      f[2 * j + 1] = t.y;
+    for (int u = 0; u < kUnroll; ++u) {
+      const int v = v0 + u * kCeThreads;
+      raws[u] = (v < nvec) ? __ldg(reinterpret_cast<const uint4*>(lrow) + v) : make_uint4(0, 0, 0, 0);
     }
-    float vm = -FLT_MAX;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = v * 8 + j;
-      if (c < V) {
-        vm = fmaxf(vm, f[j]);
-        if (f[j] > best.m) { best.m = f[j]; best.i = c; }
+    for (int u = 0; u < kUnroll; ++u) {
+      const int v = v0 + u * kCeThreads;
+      if (v >= nvec) break;
+      const uint4 raw = raws[u];
+      if (kCache) row_cache[v] = raw;
+      const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 t = unpack_bf16x2(w[j]);
+        f[2 * j] = t.x;
+        f[2 * j + 1] = t.y;
       }
-    }
-    if (vm > m) { s *= __expf(m - vm); m = vm; }
+      if (v * 8 + 8 > V) {  // ragged last vector: neutralise the pad columns
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (v * 8 + j < V) s += __expf(f[j] - m);
+        for (int j = 0; j < 8; ++j)
+          if (v * 8 + j >= V) f[j] = -FLT_MAX;
+      }
+      const float vm = fmaxf(fmaxf(fmaxf(f[0], f[1]), fmaxf(f[2], f[3])), fmaxf(fmaxf(f[4], f[5]), fmaxf(f[6], f[7])));
+      if (vm > best.m) {  // rare after the first few vectors; first max wins inside the vector
+        best.m = vm;
+#pragma unroll
+        for (int j = 7; j >= 0; --j)
+          if (f[j] == vm) best.i = v * 8 + j;
+      }
+      if (vm > m) { s *= ex2_approx((m - vm) * kLog2eF); m = vm; }
+      const float mb = m * kLog2eF;
+      float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; j += 2) {
+        acc0 += ex2_approx(fmaf(f[j], kLog2eF, -mb));      // pad columns: exp2(-huge) = 0
+        acc1 += ex2_approx(fmaf(f[j + 1], kLog2eF, -mb));
+      }
+      s += acc0 + acc1;
+    }
   }
   // warp reduce
 #pragma unroll
@@ -110,13 +136,21 @@ softmax_ce_kernel(const __nv_bfloat16* __restrict__ logits, const int32_t* __res
       g[2 * j] = t.x;
       g[2 * j + 1] = t.y;
     }
+    const float lse2 = lse * kLog2eF;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = v * 8 + j;
-      float p = (c < V) ? __expf(g[j] - lse) : 0.f;
-      if (c == label) p -= 1.f;
-      g[j] = p * grad_scale;
+    for (int j = 0; j < 8; ++j) g[j] = ex2_approx(fmaf(g[j], kLog2eF, -lse2));
+    if (v * 8 + 8 > V) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (v * 8 + j >= V) g[j] = 0.f;
     }
+    if (v == (label >> 3)) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j == (label & 7)) g[j] -= 1.f;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= grad_scale;
     uint4 o;
     o.x = pack_bf16x2(g[0], g[1]); o.y = pack_bf16x2(g[2], g[3]);
     o.z = pack_bf16x2(g[4], g[5]); o.w = pack_bf16x2(g[6], g[7]);
