@@ -258,7 +258,7 @@ def gpu_main(args) -> None:
     from plaincv_b200 import _lib
     from plaincv_b200.engine import Engine
     from plaincv_b200.model import construct_model
-    from oracle import lm_oracle as O  # synthetic batch generator only (host data, not compute)
+    from plaincv_b200.batch import synthetic_batch
 
     c = CONFIGS[args.config]
     B, T, V = c["micro_batch"], c["seq_len"], c["vocab_size"]
@@ -267,7 +267,7 @@ def gpu_main(args) -> None:
     lib = _lib.load()
     tokens_per_step = B * T * world
 
-    batch = O.synthetic_batch(B, T, V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
+    batch = synthetic_batch(B, T, V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
     inputs_h, labels_h, ds_h = eng_prepare(eng, batch)
     inputs_d, labels_d = inputs_h.to(dev), labels_h.to(dev)
     ds_d = None if ds_h is None else ds_h.to(dev)

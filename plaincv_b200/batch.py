@@ -93,3 +93,26 @@ def shard_for_rank(x: Optional[torch.Tensor], rank: int, world_size: int) -> Opt
         raise ValueError(f"Leading batch dimension {x.shape[0]} is not divisible by n_devices={world_size}.")
     per = x.shape[0] // world_size
     return x[rank * per: (rank + 1) * per]
+
+
+def synthetic_batch(batch_size: int, seq_len: int, vocab_size: int, seed: int = 1234,
+                    doc_mean: Optional[int] = None) -> dict:
+    """A synthetic batch in the loader's contract (data/lm_loader.py:32-38): `input_ids` int32 [B, T+1] uniform in
+    [0, V) and, when doc_mean is given, `docs_lengths` (list per row, summing to T+1, exponential lengths — the shape
+    of concat_chunck's output, data_prep_utils.py:117-141).  The reference has no synthetic-data mode (README TODO);
+    bench.py and the tests feed this straight into the _prepare_batch contract."""
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(0, vocab_size, (batch_size, seq_len + 1), generator=g, dtype=torch.int64)
+    batch = {"input_ids": ids.numpy().astype(np.int32)}
+    if doc_mean is not None:
+        rng = np.random.default_rng(seed + 4321)
+        docs = []
+        for _ in range(batch_size):
+            lens, left = [], seq_len + 1
+            while left > 0:
+                n = int(min(left, max(1, round(rng.exponential(doc_mean)))))
+                lens.append(n)
+                left -= n
+            docs.append(lens)
+        batch["docs_lengths"] = docs
+    return batch

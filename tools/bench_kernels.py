@@ -21,7 +21,7 @@ flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 res = {}
 
 
-def timeit(fn, iters=10, warm=3):
+def timeit(fn, iters=int(os.environ.get('PCV_KB_ITERS', 10)), warm=int(os.environ.get('PCV_KB_WARM', 3))):
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
