@@ -35,10 +35,15 @@ long long pcv_launch_count(void);
 
 /* C[M,N] (=|+=) alpha * sum_k A(m,k) B(n,k); bf16 operands, fp32 accumulate (tcgen05 / TMEM).
  * a_mn_major = 0: A stored [M][lda] (k contiguous); 1: A stored [K][lda] (m contiguous).  Same for B with N.
+ * splits: split-K factor (PCV_EPI_F32_ATOMIC only; 0 = let the library pick one that fills whole waves).
  * Replaces flax.linen.Dense on the hot path — models/LM/transformer.py:110-134 (fc_gate/fc_up/fc2),
  * :194-201 (w_qkv), :246-253 (w_out), :398-405 (lm_head) — and their autodiff transposes (train_lm.py:267). */
 int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                   int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream);
+
+/* Tiling override for tests and benchmarks: 0 = automatic (CTA-pair 256x256 tiles, tcgen05 cta_group::2, whenever they
+ * fill the machine; single-CTA 128xBN tiles otherwise), 1 = single-CTA tiles only, 2 = CTA-pair tiles always. */
+int pcv_gemm_set_mode(int mode);
 
 /* fp32 master -> bf16 compute copy, zero-filling the padded tail columns: dst[rows][dst_ld] <- src[rows][src_ld][:cols].
  * Replaces flax's per-call promote_dtype of `kernel`/`embedding` (transformer.py: every nn.Dense / nn.Embed). */

@@ -248,7 +248,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
     for (int j = jlo; j <= jhi; ++j, ++idx) {
       const int slot = idx % 3;
       const uint32_t use_par = (idx / 3) & 1;
+      TRACE(6, idx * 3 + 0);
       mbar_wait(bKVempty(slot), use_par ^ 1u);
+      TRACE(6, idx * 3 + 1);
       if (ltid == 0) {
         mbar_expect_tx(bVfull(slot), kTileBytes);
         tma_load_2d(sV + slot * kTileBytes, &tm_qkv, bVfull(slot), 2 * d + h * 64, static_cast<int>(seq_row0) + j * 128);
@@ -256,6 +258,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
       load_rope_tile(sK + slot * kTileBytes, kcol, ld, seq_row0 + j * 128, j * 128, T, cos_sin, ltid);
       fence_proxy_async_smem();
       mbar_arrive(bKready(slot));
+      TRACE(6, idx * 3 + 2);
     }
   } else if (warp == 12) {
     // ============================== MMA issuer ==============================

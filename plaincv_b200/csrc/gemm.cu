@@ -67,6 +67,42 @@ __device__ __forceinline__ void decode_work(const GemmParams& p, int w, int& m_b
   n_blk = r / gm;
 }
 
+
+// One thread's 32 consecutive accumulator columns of one output row -> global memory.
+template <int EPI>
+__device__ __forceinline__ void store_row_chunk(const GemmParams& p, int row, int col0, const uint32_t* r) {
+  if constexpr (EPI == PCV_EPI_BF16) {
+    __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      if (col0 + v * 8 + 8 <= p.N) {
+        uint4 o;
+        o.x = pack_bf16x2(__uint_as_float(r[v * 8 + 0]) * p.alpha, __uint_as_float(r[v * 8 + 1]) * p.alpha);
+        o.y = pack_bf16x2(__uint_as_float(r[v * 8 + 2]) * p.alpha, __uint_as_float(r[v * 8 + 3]) * p.alpha);
+        o.z = pack_bf16x2(__uint_as_float(r[v * 8 + 4]) * p.alpha, __uint_as_float(r[v * 8 + 5]) * p.alpha);
+        o.w = pack_bf16x2(__uint_as_float(r[v * 8 + 6]) * p.alpha, __uint_as_float(r[v * 8 + 7]) * p.alpha);
+        *reinterpret_cast<uint4*>(crow + v * 8) = o;
+      }
+    }
+  } else {
+    float* crow = reinterpret_cast<float*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
+#pragma unroll
+    for (int v = 0; v < 8; ++v) {
+      if (col0 + v * 4 + 4 <= p.N) {
+        const float x0 = __uint_as_float(r[v * 4 + 0]) * p.alpha, x1 = __uint_as_float(r[v * 4 + 1]) * p.alpha;
+        const float x2 = __uint_as_float(r[v * 4 + 2]) * p.alpha, x3 = __uint_as_float(r[v * 4 + 3]) * p.alpha;
+        if constexpr (EPI == PCV_EPI_F32_ATOMIC) {
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(crow + v * 4), "f"(x0), "f"(x1),
+                       "f"(x2), "f"(x3)
+                       : "memory");
+        } else {
+          *reinterpret_cast<float4*>(crow + v * 4) = make_float4(x0, x1, x2, x3);
+        }
+      }
+    }
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -205,38 +241,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         tmem_ld_32x32b_x32(taddr + c * 32, r);
         tmem_ld_wait();
         const int col0 = n0 + c * 32;
-        if (row < p.M && col0 < p.N) {
-          if constexpr (EPI == PCV_EPI_BF16) {
-            __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
-#pragma unroll
-            for (int v = 0; v < 4; ++v) {
-              if (col0 + v * 8 + 8 <= p.N) {
-                uint4 o;
-                o.x = pack_bf16x2(__uint_as_float(r[v * 8 + 0]) * p.alpha, __uint_as_float(r[v * 8 + 1]) * p.alpha);
-                o.y = pack_bf16x2(__uint_as_float(r[v * 8 + 2]) * p.alpha, __uint_as_float(r[v * 8 + 3]) * p.alpha);
-                o.z = pack_bf16x2(__uint_as_float(r[v * 8 + 4]) * p.alpha, __uint_as_float(r[v * 8 + 5]) * p.alpha);
-                o.w = pack_bf16x2(__uint_as_float(r[v * 8 + 6]) * p.alpha, __uint_as_float(r[v * 8 + 7]) * p.alpha);
-                *reinterpret_cast<uint4*>(crow + v * 8) = o;
-              }
-            }
-          } else {
-            float* crow = reinterpret_cast<float*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
-#pragma unroll
-            for (int v = 0; v < 8; ++v) {
-              if (col0 + v * 4 + 4 <= p.N) {
-                const float x0 = __uint_as_float(r[v * 4 + 0]) * p.alpha, x1 = __uint_as_float(r[v * 4 + 1]) * p.alpha;
-                const float x2 = __uint_as_float(r[v * 4 + 2]) * p.alpha, x3 = __uint_as_float(r[v * 4 + 3]) * p.alpha;
-                if constexpr (EPI == PCV_EPI_F32_ATOMIC) {
-                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(crow + v * 4), "f"(x0), "f"(x1),
-                               "f"(x2), "f"(x3)
-                               : "memory");
-                } else {
-                  *reinterpret_cast<float4*>(crow + v * 4) = make_float4(x0, x1, x2, x3);
-                }
-              }
-            }
-          }
-        }
+        if (row < p.M && col0 < p.N) store_row_chunk<EPI>(p, row, col0, r);
       }
       tc_fence_before();
       __syncwarp();
@@ -249,6 +254,185 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------ CTA-pair kernel
+// Two CTAs (a cluster of 2 = one TPC) cooperate on a 256 x 256 output tile with tcgen05 cta_group::2:
+//   CTA r stages rows [r*128, r*128+128) of the A tile and rows [r*128, r*128+128) of the B tile (half of N each);
+//   one thread of the leader CTA issues 256 x 256 x 16 MMAs that read A/B from both CTAs' shared memory and
+//   accumulate into both CTAs' tensor memory (128 lanes each); each CTA's epilogue warps drain their own half.
+// Per k-block a CTA pulls 32 KB for 2*128*256*64 flop: 128 flop per L2 byte against 85 for the single-CTA
+// 128 x 256 tile — the single-CTA kernel saturates the L2 -> SM fabric (~12 TB/s) near 1.1 PFLOP/s.
+struct PairCfg {
+  static constexpr int kBN = 256;
+  static constexpr int kTileM = 256;
+  static constexpr int kStages = 6;
+  static constexpr int kABytes = 128 * kBK * 2;  // this CTA's 128 rows of A
+  static constexpr int kBBytes = 128 * kBK * 2;  // this CTA's 128 of the 256 B rows
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;
+  static constexpr uint32_t kTmemCols = 512;  // two 256-column accumulators
+};
+
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                      const GemmParams p) {
+  using Cfg = PairCfg;
+  constexpr int BN = Cfg::kBN;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t smem_a = smem_base;
+  const uint32_t smem_b = smem_base + Cfg::kStages * Cfg::kABytes;
+  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
+  auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + s); };
+  auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + 2 + s); };
+  const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * Cfg::kStages + 4);
+  volatile uint32_t* tmem_ptr_generic =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+  const int npairs = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(full_bar(s), 1);   // leader: its producer's arrive.expect_tx (bytes of BOTH CTAs)
+      mbar_init(empty_bar(s), 1);  // multicast tcgen05.commit
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tmem_full_bar(s), 1);   // multicast tcgen05.commit
+      mbar_init(tmem_empty_bar(s), 8);  // leader: 4 epilogue warps of each CTA
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_pair<Cfg::kTmemCols>(tmem_ptr_smem);
+  }
+  tc_fence_before();
+  cluster_sync_all();  // barriers of both CTAs initialised, both TMEM allocations done
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_generic;
+
+  const int total_work = p.m_tiles * p.n_tiles * p.splits;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer (both CTAs; completion lands on the leader's barrier) =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = pair; w < total_work; w += npairs) {
+        int m_blk, n_blk, split;
+        decode_work(p, w, m_blk, n_blk, split);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const int m0 = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128;
+        const int n0 = n_blk * BN + static_cast<int>(rank) * 128;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * Cfg::kStageBytes);
+          const uint32_t bar = mapa_shared(full_bar(stage), 0);
+          const uint32_t sa = smem_a + stage * Cfg::kABytes;
+          const uint32_t sb = smem_b + stage * Cfg::kBBytes;
+          const int k0 = kb * kBK;
+          if constexpr (!A_MN) {
+            tma_load_2d_pair(sa, &tma_a, bar, k0, m0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) tma_load_2d_pair(sa + i * (64 * kBK * 2), &tma_a, bar, m0 + 64 * i, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_pair(sb, &tma_b, bar, k0, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) tma_load_2d_pair(sb + i * (64 * kBK * 2), &tma_b, bar, n0 + 64 * i, k0);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0 && rank == 0) {
+      // ===================== MMA issuer (leader CTA only) =====================
+      constexpr uint32_t idesc = umma_idesc_bf16(256, BN, A_MN, B_MN);
+      constexpr uint32_t a_kstep = A_MN ? 16 * 128 : 32;
+      constexpr uint32_t b_kstep = B_MN ? 16 * 128 : 32;
+      constexpr uint32_t a_lbo = A_MN ? 64 * kBK * 2 : 16, b_lbo = B_MN ? 64 * kBK * 2 : 16;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int w = pair; w < total_work; w += npairs, ++it) {
+        const int split = w / (p.n_tiles * p.m_tiles);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(tmem_empty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_a + stage * Cfg::kABytes;
+          const uint32_t sb = smem_b + stage * Cfg::kBBytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024);
+            const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024);
+            umma_bf16_ss_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit_pair(empty_bar(stage), 3);  // frees this smem slot in both CTAs
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit_pair(tmem_full_bar(acc), 3);  // accumulator complete -> both CTAs' epilogues
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue (each CTA drains its own 128 accumulator rows) =====================
+    const int ew = warp & 3;
+    int it = 0;
+    for (int w = pair; w < total_work; w += npairs, ++it) {
+      int m_blk, n_blk, split_unused;
+      decode_work(p, w, m_blk, n_blk, split_unused);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tmem_full_bar(acc), acc_phase);
+      tc_fence_after();
+      const int row = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128 + ew * 32 + lane;
+      const int n0 = n_blk * BN;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        if (row < p.M && col0 < p.N) store_row_chunk<EPI>(p, row, col0, r);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_shared(tmem_empty_bar(acc), 0));
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // the peer's MMAs/TMEM reads are finished before either CTA releases TMEM or exits
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
   }
 }
 
@@ -386,16 +570,109 @@ static int dispatch_major(int a_mn, int b_mn, int epi, const CUtensorMap& ta, co
   return dispatch_epi<BN, true, true>(epi, ta, tb, p, grid, st);
 }
 
+
+template <bool A_MN, bool B_MN, int EPI>
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                            cudaStream_t st) {
+  auto kern = gemm_bf16_pair_kernel<A_MN, B_MN, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg::kSmemBytes);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_set = true;
+  }
+  kern<<<grid, kGemmThreads, PairCfg::kSmemBytes, st>>>(ta, tb, p);  // __cluster_dims__(2,1,1): grid is even
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
+}
+
+template <bool A_MN, bool B_MN>
+static int dispatch_epi_pair(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
+                             cudaStream_t st) {
+  switch (epi) {
+    case PCV_EPI_BF16: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_BF16>(ta, tb, p, grid, st);
+    case PCV_EPI_F32_ATOMIC: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32_ATOMIC>(ta, tb, p, grid, st);
+    case PCV_EPI_F32: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32>(ta, tb, p, grid, st);
+  }
+  return PCV_ERR_ARG;
+}
+
+static int dispatch_major_pair(int a_mn, int b_mn, int epi, const CUtensorMap& ta, const CUtensorMap& tb,
+                               const GemmParams& p, int grid, cudaStream_t st) {
+  if (!a_mn && !b_mn) return dispatch_epi_pair<false, false>(epi, ta, tb, p, grid, st);
+  if (!a_mn && b_mn) return dispatch_epi_pair<false, true>(epi, ta, tb, p, grid, st);
+  if (a_mn && !b_mn) return dispatch_epi_pair<true, false>(epi, ta, tb, p, grid, st);
+  return dispatch_epi_pair<true, true>(epi, ta, tb, p, grid, st);
+}
+
+
+// Split-K factor for the accumulate-into-fp32 (wgrad) GEMMs: the one that fills whole waves of CTA pairs best while
+// keeping >= 16 k-blocks per split; ties go to the smaller factor (less red.add traffic).
+static int auto_splits(int M, int N, int K) {
+  const int pairs = num_sms() / 2;
+  const long tiles = static_cast<long>((M + 255) / 256) * ((N + 255) / 256);
+  const int kb = (K + kBK - 1) / kBK;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= 16; ++s) {
+    if (s > 1 && kb / s < 16) break;
+    const long work = tiles * s;
+    const long waves = (work + pairs - 1) / pairs;
+    const double eff = static_cast<double>(work) / static_cast<double>(waves * pairs);
+    if (eff > best_eff + 0.02) { best_eff = eff; best = s; }
+  }
+  return best;
+}
+
+static int g_gemm_mode = 0;  // 0 auto, 1 single-CTA tiles only, 2 CTA-pair tiles whenever legal
+
 }  // namespace pcv
+
+extern "C" int pcv_gemm_set_mode(int mode) {
+  if (mode < 0 || mode > 2) return PCV_ERR_ARG;
+  pcv::g_gemm_mode = mode;
+  return PCV_OK;
+}
 
 extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                              int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream) {
   using namespace pcv;
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return PCV_ERR_ARG;
-  if (splits < 1) splits = 1;
+  if (splits < 0) return PCV_ERR_ARG;
+  if (splits == 0) splits = (epilogue == PCV_EPI_F32_ATOMIC) ? auto_splits(M, N, K) : 1;
   if (epilogue != PCV_EPI_F32_ATOMIC && splits != 1) return PCV_ERR_ARG;
   const int vec = (epilogue == PCV_EPI_BF16) ? 8 : 4;
   if (N % vec || ldc % vec || (reinterpret_cast<uintptr_t>(C) & 15)) return PCV_ERR_ALIGN;
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int kb_total = (K + kBK - 1) / kBK;
+  // CTA-pair 256 x 256 tiles whenever they can occupy every SM pair at least once; otherwise single-CTA tiles.
+  {
+    const int m2 = (M + 255) / 256, n2 = (N + 255) / 256;
+    const int kps = (kb_total + splits - 1) / splits;
+    const int sp = (kb_total + kps - 1) / kps;
+    const long t2 = static_cast<long>(m2) * n2 * sp;
+    const bool pair = g_gemm_mode == 2 || (g_gemm_mode == 0 && t2 >= num_sms() / 2);
+    if (pair) {
+      CUtensorMap ta, tb;
+      int rc;
+      if (!a_mn_major) rc = get_tmap_2d_bf16(&ta, A, M, K, lda, 128);
+      else rc = get_tmap_2d_bf16(&ta, A, K, M, lda, 64);
+      if (rc) return rc;
+      if (!b_mn_major) rc = get_tmap_2d_bf16(&tb, B, N, K, ldb, 128);
+      else rc = get_tmap_2d_bf16(&tb, B, K, N, ldb, 64);
+      if (rc) return rc;
+      GemmParams p;
+      p.C = C;
+      p.M = M; p.N = N; p.K = K; p.ldc = ldc;
+      p.m_tiles = m2; p.n_tiles = n2;
+      p.kb_total = kb_total; p.kb_per_split = kps; p.splits = sp;
+      p.alpha = alpha;
+      const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
+      count_launch();
+      return dispatch_major_pair(a_mn_major, b_mn_major, epilogue, ta, tb, p, static_cast<int>(2 * pairs), st);
+    }
+  }
 
   // tile-N choice: 256 unless the problem cannot fill the machine with 128x256 tiles
   const int m_tiles = (M + kBM - 1) / kBM;
@@ -418,13 +695,12 @@ extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.M = M; p.N = N; p.K = K; p.ldc = ldc;
   p.m_tiles = m_tiles;
   p.n_tiles = (N + BN - 1) / BN;
-  p.kb_total = (K + kBK - 1) / kBK;
+  p.kb_total = kb_total;
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.alpha = alpha;
   const long total = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   count_launch();
   if (BN == 256) return dispatch_major<256>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
   return dispatch_major<128>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);

@@ -89,28 +89,44 @@ static int run_case(int M, int N, int K, int a_mn, int b_mn, int epi, int splits
 int main(int argc, char** argv) {
   int fails = 0;
   const bool quick = argc > 1 && atoi(argv[1]) == 1;
-  // smallest first: one tile, one k-block, K-major/K-major
-  fails += run_case(128, 128, 64, 0, 0, PCV_EPI_F32, 1, false);
-  fails += run_case(128, 256, 64, 0, 0, PCV_EPI_F32, 1, false);
-  fails += run_case(128, 128, 256, 0, 0, PCV_EPI_F32, 1, false);
-  fails += run_case(128, 128, 64, 0, 1, PCV_EPI_F32, 1, false);
-  fails += run_case(128, 128, 64, 1, 0, PCV_EPI_F32, 1, false);
-  fails += run_case(128, 128, 64, 1, 1, PCV_EPI_F32, 1, false);
-  if (quick) return fails;
-  for (int a_mn = 0; a_mn < 2; ++a_mn)
-    for (int b_mn = 0; b_mn < 2; ++b_mn) {
-      fails += run_case(256, 384, 192, a_mn, b_mn, PCV_EPI_BF16, 1, false);
-      fails += run_case(200, 136, 72, a_mn, b_mn, PCV_EPI_F32, 1, false);       // ragged M/N/K tails
-      fails += run_case(1000, 2736, 1000, a_mn, b_mn, PCV_EPI_BF16, 1, false);  // several tiles per CTA? no: < 148
-      fails += run_case(384, 520, 2000, a_mn, b_mn, PCV_EPI_F32_ATOMIC, 4, false);
-    }
-  // persistent path (more tiles than SMs) + timing at the 420M shapes
-  fails += run_case(16384, 3072, 1024, 0, 1, PCV_EPI_BF16, 1, true);     // fwd  QKV
-  fails += run_case(16384, 1024, 3072, 0, 0, PCV_EPI_BF16, 1, true);     // dgrad QKV
-  fails += run_case(1024, 3072, 16384, 1, 1, PCV_EPI_F32_ATOMIC, 4, true);  // wgrad QKV
-  fails += run_case(16384, 5472, 1024, 0, 1, PCV_EPI_BF16, 1, true);     // fwd gate/up
-  fails += run_case(16384, 1024, 2736, 0, 1, PCV_EPI_BF16, 1, true);     // fwd down
-  fails += run_case(8192, 8192, 8192, 0, 0, PCV_EPI_BF16, 1, true);      // the cuBLAS peak shape
+  const bool notime = argc > 1 && atoi(argv[1]) == 2;
+  for (int mode = 1; mode <= 2; ++mode) {  // 1: single-CTA tiles, 2: CTA-pair (cta_group::2) tiles
+    pcv_gemm_set_mode(mode);
+    printf("---- gemm mode %d (%s)\n", mode, mode == 1 ? "single-CTA 128xBN" : "CTA pair 256x256");
+    // smallest first: one tile, one k-block, K-major/K-major
+    fails += run_case(128, 128, 64, 0, 0, PCV_EPI_F32, 1, false);
+    fails += run_case(256, 256, 64, 0, 0, PCV_EPI_F32, 1, false);
+    fails += run_case(128, 128, 256, 0, 0, PCV_EPI_F32, 1, false);
+    fails += run_case(256, 256, 64, 0, 1, PCV_EPI_F32, 1, false);
+    fails += run_case(256, 256, 64, 1, 0, PCV_EPI_F32, 1, false);
+    fails += run_case(256, 256, 64, 1, 1, PCV_EPI_F32, 1, false);
+    if (quick) continue;
+    for (int a_mn = 0; a_mn < 2; ++a_mn)
+      for (int b_mn = 0; b_mn < 2; ++b_mn) {
+        fails += run_case(256, 384, 192, a_mn, b_mn, PCV_EPI_BF16, 1, false);
+        fails += run_case(200, 136, 72, a_mn, b_mn, PCV_EPI_F32, 1, false);       // ragged M/N/K tails
+        fails += run_case(1000, 2736, 1000, a_mn, b_mn, PCV_EPI_BF16, 1, false);
+        fails += run_case(384, 520, 2000, a_mn, b_mn, PCV_EPI_F32_ATOMIC, 4, false);
+        fails += run_case(3000, 5472, 520, a_mn, b_mn, PCV_EPI_BF16, 1, false);   // several tiles per CTA (pair)
+      }
+  }
+  if (quick) { printf("%s (%d failing cases)\n", fails ? "GEMM TEST FAILED" : "GEMM TEST PASSED", fails); return fails; }
+  // persistent path + timing at the 420M shapes, both tilings
+  for (int mode = 1; mode <= 2 && !notime; ++mode) {
+    pcv_gemm_set_mode(mode);
+    printf("---- timing, gemm mode %d\n", mode);
+    fails += run_case(16384, 3072, 1024, 0, 1, PCV_EPI_BF16, 1, true);     // fwd  QKV
+    fails += run_case(16384, 1024, 3072, 0, 0, PCV_EPI_BF16, 1, true);     // dgrad QKV
+    fails += run_case(1024, 3072, 16384, 1, 1, PCV_EPI_F32_ATOMIC, mode == 1 ? 4 : 3, true);  // wgrad QKV
+    fails += run_case(16384, 1024, 1024, 0, 1, PCV_EPI_BF16, 1, true);     // fwd out-proj
+    fails += run_case(16384, 5472, 1024, 0, 1, PCV_EPI_BF16, 1, true);     // fwd gate/up
+    fails += run_case(16384, 1024, 2736, 0, 1, PCV_EPI_BF16, 1, true);     // fwd down
+    fails += run_case(1024, 5472, 16384, 1, 1, PCV_EPI_F32_ATOMIC, mode == 1 ? 4 : 2, true);  // wgrad gate/up
+    fails += run_case(16384, 50280, 1024, 0, 1, PCV_EPI_BF16, 1, true);    // LM head fwd
+    fails += run_case(16384, 1024, 50280, 0, 0, PCV_EPI_BF16, 1, true);    // LM head dgrad
+    fails += run_case(8192, 8192, 8192, 0, 0, PCV_EPI_BF16, 1, true);      // the cuBLAS peak shape
+  }
+  pcv_gemm_set_mode(0);
   printf("%s (%d failing cases)\n", fails ? "GEMM TEST FAILED" : "GEMM TEST PASSED", fails);
   return fails;
 }

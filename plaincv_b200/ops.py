@@ -61,18 +61,11 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, alpha: float = 1.0) -> torch
     return dx
 
 
-def wgrad_splits(k_in: int, n_out: int, tokens: int) -> int:
-    tiles = ((k_in + 127) // 128) * ((n_out + 255) // 256)
-    kb = (tokens + 63) // 64
-    s = max(1, -(-2 * _NUM_SMS // tiles))
-    return max(1, min(s, kb // 8 if kb >= 8 else 1))
-
-
 def linear_wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, alpha: float = 1.0) -> None:
-    """dw[K,Np] (fp32) += x[M,K]^T @ dy[M,Np]  (split-K, red.add epilogue)."""
+    """dw[K,Np] (fp32) += x[M,K]^T @ dy[M,Np]  (split-K, red.add epilogue; split factor picked by the library)."""
     M, K = x.shape
     Np = dy.shape[1]
-    gemm(x, dy, dw, K, Np, M, K, Np, Np, True, True, PCV_EPI_F32_ATOMIC, wgrad_splits(K, Np, M), alpha)
+    gemm(x, dy, dw, K, Np, M, K, Np, Np, True, True, PCV_EPI_F32_ATOMIC, 0, alpha)  # splits=0: chosen by the library
 
 
 def cast_pad_bf16(src: torch.Tensor, dst: torch.Tensor, rows: int, cols: int, src_ld: int, dst_ld: int) -> None:

@@ -32,6 +32,10 @@ for w in range(2):
     print(f"--- MMA waits for P of WG{w}: [wait cycles] @abs")
     print([(int(m[i * 2 + 1] - m[i * 2]), int(m[i * 2] - t0)) for i in range(16)])
 
+ld = a[6]
+print("--- fwd loader (thread 256): per K tile [wait empty slot, load+rope+store] @abs")
+print([(int(ld[i * 3 + 1] - ld[i * 3]), int(ld[i * 3 + 2] - ld[i * 3 + 1]), int(ld[i * 3] - t0)) for i in range(16)])
+
 # ---- backward
 dout = torch.randn(B * T, d, device="cuda").to(torch.bfloat16)
 for _ in range(2):
