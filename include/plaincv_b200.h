@@ -70,17 +70,26 @@ int pcv_rmsnorm_residual_bwd(const void* dy, const void* dres_out, const void* r
 int pcv_swiglu_fwd(const void* gu, void* h, int M, int hid, void* stream);
 int pcv_swiglu_bwd(const void* gu, const void* dh, void* dgu, int M, int hid, void* stream);
 
-/* Flash-style attention over qkv[B*T][3*d] (columns [q|k|v], each head-major [N][hd], hd = 64) with interleaved-pair
- * RoPE applied to q and k on load (models/LM/embedding.py:28-67; cos_sin = fp32 [T][32][2] = (cos, sin) of
- * precompute_freqs_cis, embedding.py:8-26, built once by the host) and softmax(q k^T / sqrt(hd) + mask) v
+/* Y[M,N] = bf16( rope( X[M,K] @ W[K,N] ) ): the w_qkv Dense (models/LM/transformer.py:194-201) with the interleaved-pair
+ * RoPE of models/LM/embedding.py:28-67 applied in the epilogue to output columns [0, rope_cols) (the q | k thirds,
+ * head_dim 64) at position (row % T), in fp32 before the bf16 rounding.  cos_sin = fp32 [T][32][2] = (cos, sin) of
+ * precompute_freqs_cis (embedding.py:8-26), built once by the host. */
+int pcv_gemm_bf16_rope(const void* X, const void* W, void* Y, int M, int N, int K, int ldx, int ldw, int ldy,
+                       const float* cos_sin, int T, int rope_cols, void* stream);
+/* The same rotation as a stand-alone in-place pass over the q | k columns of qkv[B*T][3*d]. */
+int pcv_rope_qk(void* qkv, const float* cos_sin, int B, int T, int n_heads, void* stream);
+
+/* Flash-style attention over qkv[B*T][3*d] (columns [q|k|v], each head-major [N][hd], hd = 64; q and k ALREADY
+ * rotated by pcv_gemm_bf16_rope / pcv_rope_qk): softmax(q k^T / sqrt(hd) + mask) v
  * (jax.nn.dot_product_attention at models/LM/transformer.py:233-240).  Mask: causal, intersected with document
  * blocks when doc_start != NULL (doc_start[b*T + t] = first position of the document containing t; the
  * block-diagonal mask of data/datasets/data_prep_utils.py:14-43, never materialised).
- * out[B*T][d] bf16; lse[B][N][T] fp32 saved for backward. */
-int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, void* out, float* lse, int B, int T,
-                 int n_heads, void* stream);
-/* dqkv[B*T][3*d] from dout.  Scratch supplied by the caller: delta[B][N][T] fp32 (rowsum(dout*out)) and
- * dq_acc[B*T][d] fp32 (zeroed here; dQ partials of the key tiles are red.add-ed into it, then un-rotated). */
+ * out[B*T][d] bf16; lse[B][N][T] fp32 saved for backward.  T must be a multiple of 128. */
+int pcv_attn_fwd(const void* qkv, const int32_t* doc_start, void* out, float* lse, int B, int T, int n_heads,
+                 void* stream);
+/* dqkv[B*T][3*d] (gradient w.r.t. the UN-rotated qkv: the transpose of the rotation is applied to dq and dk here)
+ * from dout.  Scratch supplied by the caller: delta[B][N][T] fp32 (rowsum(dout*out)) and dq_acc[B*T][d] fp32
+ * (zeroed here; dQ partials of the key tiles are reduce-added into it, then un-rotated). */
 int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out, const void* dout,
                  const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int n_heads, void* stream);
 

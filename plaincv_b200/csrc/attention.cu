@@ -39,7 +39,7 @@ __device__ long long g_trace[8192];
 #define TRACE(slot, idx) do { } while (0)
 #endif
 
-constexpr int kAttnThreads = 416;
+constexpr int kAttnThreads = 320;
 constexpr int kTileBytes = 128 * 128;  // 128 rows x 64 bf16
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kSoftmaxScale = 0.125f;  // 1/sqrt(64)
@@ -71,38 +71,6 @@ __device__ __forceinline__ uint4 rope_chunk(uint4 raw, float4 cs0, float4 cs1, f
   o.z = pack_bf16x2(p2.x * cs1.x - sign * p2.y * cs1.y, p2.y * cs1.x + sign * p2.x * cs1.y);
   o.w = pack_bf16x2(p3.x * cs1.z - sign * p3.y * cs1.w, p3.y * cs1.z + sign * p3.x * cs1.w);
   return o;
-}
-
-// 128 threads (ltid 0..127) load rows [t0, t0+128) x 64 columns of one sequence, apply RoPE at position t, and store
-// the tile 128B-swizzled.  8 lanes cover one 128-byte row (coalesced), 16 rows per step.  Rows >= T are zero-filled.
-__device__ __forceinline__ void load_rope_tile(uint32_t smem_tile, const __nv_bfloat16* __restrict__ gcol, int ld,
-                                               long grow0, int t0, int T, const float* __restrict__ cos_sin, int ltid) {
-  const int c = ltid & 7, rsub = ltid >> 3;
-  // all 8 row loads are issued before any is consumed (one memory round trip per tile, not eight)
-  uint4 raw[8];
-#pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int r = it * 16 + rsub;
-    raw[it] = (t0 + r < T) ? ld_global_nc_v4(gcol + (grow0 + r) * ld + c * 8) : make_uint4(0, 0, 0, 0);
-  }
-#pragma unroll
-  for (int half = 0; half < 2; ++half) {
-    float4 cs[4][2];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int t = min(t0 + (half * 4 + k) * 16 + rsub, T - 1);
-      const float4* p = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(t) * 32 + c * 4) * 2);
-      cs[k][0] = __ldg(p);
-      cs[k][1] = __ldg(p + 1);
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int it = half * 4 + k;
-      const int r = it * 16 + rsub;
-      const uint4 v = rope_chunk(raw[it], cs[k][0], cs[k][1], 1.f);
-      st_shared_v4(smem_tile + r * 128 + ((c ^ (r & 7)) << 4), v);
-    }
-  }
 }
 
 // ---- softmax chunk helpers (32 score columns held by one thread).  MASK variants take the valid column window
@@ -165,33 +133,66 @@ struct AttnFwdSmem {
   static constexpr int kBytes = kBar + 256 + 1024;
 };
 
+// 32 score columns of one row: p = exp2(s*c2 - mb) (0 outside [lo, hi] when MASK), packed to bf16 pairs.
+// Accumulates the row sum into `sum2` (two partial sums) and, when TRACK, the largest valid score into `smax`.
+// Packed fp32x2 FMA / ADD halve the issue slots next to the one MUFU op per element.
+template <bool MASK, bool TRACK>
+__device__ __forceinline__ void chunk_softmax(const uint32_t* sr, float c2, float mb, int lo, int hi, uint32_t* packed,
+                                              float2& sum2, float& smax) {
+  const float2 c2v = make_float2(c2, c2), mbv = make_float2(-mb, -mb);
+#pragma unroll
+  for (int k = 0; k < 32; k += 2) {
+    const float s0 = __uint_as_float(sr[k]), s1 = __uint_as_float(sr[k + 1]);
+    const float2 x = __ffma2_rn(make_float2(s0, s1), c2v, mbv);
+    float e0 = ex2f(x.x), e1 = ex2f(x.y);
+    if (MASK) {
+      const bool v0 = (k >= lo && k <= hi), v1 = (k + 1 >= lo && k + 1 <= hi);
+      e0 = v0 ? e0 : 0.f;
+      e1 = v1 ? e1 : 0.f;
+      if (TRACK) smax = fmaxf(smax, fmaxf(v0 ? s0 : -INFINITY, v1 ? s1 : -INFINITY));
+    } else if (TRACK) {
+      smax = fmaxf(smax, fmaxf(s0, s1));
+    }
+    sum2 = __fadd2_rn(sum2, make_float2(e0, e1));
+    packed[k >> 1] = pack_bf16x2(e0, e1);
+  }
+}
+
+// Forward CTA (320 threads) = one (batch, head, 256-query block); q, k in `qkv` are already rotated (RoPE is applied
+// by the QKV GEMM epilogue, pcv_gemm_bf16_rope, or by pcv_rope_qk):
+//   warps 0-3 / 4-7 : softmax warpgroup 0 / 1, one thread per query row of its 128-row tile.  One pass over S per
+//                     tile: the exponent reference is the row max of the row's first visible tile and is only moved
+//                     if a later score exceeds it by 2^60 (everything is floating point: a stale reference costs no
+//                     precision), so P.V accumulates in TMEM across key tiles with no per-tile rescale or read-back.
+//   warp 8          : TMA producer (Q once, K / V ring of 3 slots each) + TMEM allocation
+//   warp 9          : tcgen05.mma issuer: S_w = Q_w.K_j^T, O_w += P_w.V_j, ping-ponged between the warpgroups
+// TMEM: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384).
 __global__ void __launch_bounds__(kAttnThreads, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16* __restrict__ qkv,
-                const float* __restrict__ cos_sin, const int32_t* __restrict__ doc_start,
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __restrict__ doc_start,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ lse, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = sbase + AttnFwdSmem::kQ, sK = sbase + AttnFwdSmem::kK, sV = sbase + AttnFwdSmem::kV,
                  sP = sbase + AttnFwdSmem::kP, sBar = sbase + AttnFwdSmem::kBar;
-  // barrier map (8 bytes each)
-  const uint32_t bQ = sBar;                                     // q_ready            (128)
-  auto bKready = [&](int s) { return sBar + 8u * (1 + s); };    // [3]                (128)
-  auto bVfull = [&](int s) { return sBar + 8u * (4 + s); };     // [3]                (tx)
-  auto bKVempty = [&](int s) { return sBar + 8u * (7 + s); };   // [3]                (1, commit)
-  auto bSfull = [&](int w) { return sBar + 8u * (10 + w); };    // [2]                (1, commit)
-  auto bPfull = [&](int w) { return sBar + 8u * (12 + w); };    // [2]                (128)
-  auto bOfull = [&](int w, int b) { return sBar + 8u * (14 + 2 * w + b); };  // [2][2] (1, commit)
-  const uint32_t tmem_ptr_smem = sBar + 8u * 18;
+  const uint32_t bQ = sBar;                                     // (tx)
+  auto bKfull = [&](int s) { return sBar + 8u * (1 + s); };     // [3] (tx)
+  auto bVfull = [&](int s) { return sBar + 8u * (4 + s); };     // [3] (tx)
+  auto bKempty = [&](int s) { return sBar + 8u * (7 + s); };    // [3] (1, commit)
+  auto bVempty = [&](int s) { return sBar + 8u * (10 + s); };   // [3] (1, commit)
+  auto bSfull = [&](int w) { return sBar + 8u * (13 + w); };    // [2] (1, commit)
+  auto bPfull = [&](int w) { return sBar + 8u * (15 + w); };    // [2] (128)
+  auto bPVdone = [&](int w) { return sBar + 8u * (17 + w); };   // [2] (1, commit)
+  const uint32_t tmem_ptr_smem = sBar + 8u * 19;
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef PCV_TRACE
-  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 384);
+  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 288);
 #endif
   const int n_qblk = gridDim.x;
   const int qblk = n_qblk - 1 - blockIdx.x;  // heaviest (latest) query blocks first
   const int h = blockIdx.y, b = blockIdx.z;
-  const int d = NH * 64, ld = 3 * d;
+  const int d = NH * 64;
   const int q0 = qblk * 256;
   const long seq_row0 = static_cast<long>(b) * T;
 
@@ -212,55 +213,52 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
   const int jhi = jmax[1] >= 0 ? jmax[1] : jmax[0];
   auto active = [&](int w, int j) { return j >= jmin[w] && j <= jmax[w]; };
 
-  if (warp == 12 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
-    mbar_init(bQ, 128);
+    mbar_init(bQ, 1);
     for (int s = 0; s < 3; ++s) {
-      mbar_init(bKready(s), 128);
+      mbar_init(bKfull(s), 1);
       mbar_init(bVfull(s), 1);
-      mbar_init(bKVempty(s), 1);
+      mbar_init(bKempty(s), 1);
+      mbar_init(bVempty(s), 1);
     }
     for (int w = 0; w < 2; ++w) {
       mbar_init(bSfull(w), 1);
       mbar_init(bPfull(w), 128);
-      mbar_init(bOfull(w, 0), 1);
-      mbar_init(bOfull(w, 1), 1);
+      mbar_init(bPVdone(w), 1);
     }
     fence_mbar_init();
   }
-  if (warp == 11) tmem_alloc<512>(tmem_ptr_smem);
+  if (warp == 8) tmem_alloc<512>(tmem_ptr_smem);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
 
-  if (warp >= 8 && warp < 12) {
-    // ============================== loader warps ==============================
-    const int ltid = tid - 256;
-    const __nv_bfloat16* qcol = qkv + h * 64;
-    const __nv_bfloat16* kcol = qkv + d + h * 64;
-#pragma unroll
-    for (int w = 0; w < 2; ++w)
-      if (jmax[w] >= 0) load_rope_tile(sQ + w * kTileBytes, qcol, ld, seq_row0 + q0 + 128 * w, q0 + 128 * w, T, cos_sin, ltid);
-    fence_proxy_async_smem();
-    mbar_arrive(bQ);
-    int idx = 0;
-    for (int j = jlo; j <= jhi; ++j, ++idx) {
-      const int slot = idx % 3;
-      const uint32_t use_par = (idx / 3) & 1;
-      TRACE(6, idx * 3 + 0);
-      mbar_wait(bKVempty(slot), use_par ^ 1u);
-      TRACE(6, idx * 3 + 1);
-      if (ltid == 0) {
+  if (warp == 8) {
+    // ============================== TMA producer ==============================
+    if (lane == 0) {
+      const int row0 = static_cast<int>(seq_row0);
+      const int nq = jmax[1] >= 0 ? 2 : 1;
+      mbar_expect_tx(bQ, nq * kTileBytes);
+      for (int w = 0; w < nq; ++w) tma_load_2d(sQ + w * kTileBytes, &tm_qkv, bQ, h * 64, row0 + q0 + 128 * w);
+      int idx = 0;
+      for (int j = jlo; j <= jhi; ++j, ++idx) {
+        const int slot = idx % 3;
+        const uint32_t par = (idx / 3) & 1;
+        TRACE(6, idx * 3 + 0);
+        mbar_wait(bKempty(slot), par ^ 1u);
+        mbar_expect_tx(bKfull(slot), kTileBytes);
+        tma_load_2d(sK + slot * kTileBytes, &tm_qkv, bKfull(slot), d + h * 64, row0 + j * 128);
+        TRACE(6, idx * 3 + 1);
+        mbar_wait(bVempty(slot), par ^ 1u);
         mbar_expect_tx(bVfull(slot), kTileBytes);
-        tma_load_2d(sV + slot * kTileBytes, &tm_qkv, bVfull(slot), 2 * d + h * 64, static_cast<int>(seq_row0) + j * 128);
+        tma_load_2d(sV + slot * kTileBytes, &tm_qkv, bVfull(slot), 2 * d + h * 64, row0 + j * 128);
+        TRACE(6, idx * 3 + 2);
       }
-      load_rope_tile(sK + slot * kTileBytes, kcol, ld, seq_row0 + j * 128, j * 128, T, cos_sin, ltid);
-      fence_proxy_async_smem();
-      mbar_arrive(bKready(slot));
-      TRACE(6, idx * 3 + 2);
     }
-  } else if (warp == 12) {
+    __syncwarp();
+  } else if (warp == 9) {
     // ============================== MMA issuer ==============================
     if (lane == 0) {
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
@@ -274,29 +272,28 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
         }
         tc_commit(bSfull(w));
       };
-      auto issue_PV = [&](int w, int slot, int obuf) {
+      auto issue_PV = [&](int w, int slot, bool accumulate) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           // A = P_w (K-major, two 64-key atoms 16 KB apart); B = V (MN-major: one 128-byte row per key)
           const uint64_t da = umma_smem_desc(sP + w * 2 * kTileBytes + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
           const uint64_t db = umma_smem_desc(sV + slot * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tmem_base + 256 + w * 128 + obuf * 64, da, db, idesc_pv, k > 0 ? 1u : 0u);
+          umma_bf16_ss(tmem_base + 256 + w * 64, da, db, idesc_pv, (accumulate || k > 0) ? 1u : 0u);
         }
-        tc_commit(bOfull(w, obuf));
+        tc_commit(bPVdone(w));
       };
       mbar_wait(bQ, 0);
-      tc_fence_after();
-      // prologue: first S of each warpgroup active at jlo
-      mbar_wait(bKready(0), 0);
+      mbar_wait(bKfull(0), 0);
       tc_fence_after();
 #pragma unroll
       for (int w = 0; w < 2; ++w)
         if (active(w, jlo)) issue_S(w, 0);
+      tc_commit(bKempty(0));
       int idx = 0;
       for (int j = jlo; j <= jhi; ++j, ++idx) {
         const int slot = idx % 3;
-        const uint32_t use_par = (idx / 3) & 1;
-        const int last_w = active(1, j) ? 1 : 0;
+        const uint32_t par = (idx / 3) & 1;
+        const int slot1 = (idx + 1) % 3;
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
           const bool act = active(w, j);
@@ -308,18 +305,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
             TRACE(4 + w, i * 2 + 1);
           }
           if (nxt) {  // next S first: it is what the softmax warpgroup waits for
-            const int slot1 = (idx + 1) % 3;
-            mbar_wait(bKready(slot1), ((idx + 1) / 3) & 1);
+            mbar_wait(bKfull(slot1), ((idx + 1) / 3) & 1);
             tc_fence_after();
             issue_S(w, slot1);
           }
           if (act) {
-            mbar_wait(bVfull(slot), use_par);
+            mbar_wait(bVfull(slot), par);
             tc_fence_after();
-            issue_PV(w, slot, i & 1);
+            issue_PV(w, slot, i > 0);
           }
-          if (w == last_w) tc_commit(bKVempty(slot));
         }
+        if (j + 1 <= jhi) tc_commit(bKempty(slot1));  // every S that reads K(j+1) has been issued
+        tc_commit(bVempty(slot));
       }
     }
     __syncwarp();
@@ -333,13 +330,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
       const int ds_hi = doc_start ? doc_start[seq_row0 + min(q0 + 128 * w + 127, T - 1)] : 0;
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       const uint32_t tS = tmem_base + lane_off + w * 128;
-      const uint32_t tO = tmem_base + lane_off + 256 + w * 128;
+      const uint32_t tO = tmem_base + lane_off + 256 + w * 64;
       const uint32_t sPw = sP + w * 2 * kTileBytes;
       constexpr float c2 = kSoftmaxScale * kLog2e;
-      float acc[64];
-#pragma unroll
-      for (int k = 0; k < 64; ++k) acc[k] = 0.f;
-      float m_seen = -INFINITY, ref = -INFINITY, l_run = 0.f, alpha_prev = 0.f;
+      float ref = -INFINITY, l_run = 0.f;
       const int n_it = jmax[w] - jmin[w] + 1;
       for (int i = 0; i < n_it; ++i) {
         const int j = jmin[w] + i;
@@ -350,13 +344,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
         const bool need_mask = (j * 128 + 127 > q0 + 128 * w) || (j * 128 < ds_hi);
         const int key0 = j * 128;
         const int hi0 = t - key0, lo0 = ds_t - key0;  // valid key window relative to the tile start
-        // Reference for the exponent.  Exact tiles (the first one, and masked ones) take the row max in a first pass
-        // over S; every other tile re-uses the running max of the tiles before it ("lazy" reference: the result is
-        // identical after normalisation, and one TMEM pass over S is saved).  A lazy tile whose scores exceed the
-        // reference by more than 2^60 (or whose reference is still -inf) is redone exactly.
-        bool exact = (i == 0) || need_mask;
-        float ref_new = m_seen;
-        if (exact) {
+        // rows that have not seen a visible key yet take their reference from this tile's row max (first pass)
+        const bool first = __any_sync(0xffffffffu, ref == -INFINITY);
+        if (first) {
           float rmax = -INFINITY;
 #pragma unroll 1
           for (int c = 0; c < 4; ++c) {
@@ -366,27 +356,27 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
             rmax = need_mask ? chunk_rowmax<true>(sr, lo0 - c * 32, hi0 - c * 32, rmax)
                              : chunk_rowmax<false>(sr, 0, 0, rmax);
           }
-          ref_new = fmaxf(m_seen, rmax);
+          if (ref == -INFINITY) ref = rmax;
         }
         TRACE(w * 2 + 0, i * 4 + 2);
-        float psum, tile_max, alpha;
+        bool pv_waited = (i == 0);
+        bool check = !first;
+        float2 psum;
         while (true) {
-          const float ref_eff = (ref_new == -INFINITY) ? 0.f : ref_new;
-          alpha = ex2f((ref - ref_eff) * c2);  // ref = -inf -> 0
-          const float mb = ref_eff * c2;
-          psum = 0.f;
-          tile_max = -INFINITY;
+          const float mb = (ref == -INFINITY ? 0.f : ref) * c2;
+          psum = make_float2(0.f, 0.f);
+          float tile_max = -INFINITY;
 #pragma unroll 1
           for (int c = 0; c < 4; ++c) {
             uint32_t sr[32];
             tmem_ld_32x32b_x32(tS + c * 32, sr);
             tmem_ld_wait();
             uint32_t pk[16];
-            if (need_mask) {
-              psum += chunk_exp_pack<true>(sr, c2, mb, lo0 - c * 32, hi0 - c * 32, pk);
-            } else {
-              psum += chunk_exp_pack<false>(sr, c2, mb, 0, 0, pk);
-              if (!exact) tile_max = chunk_rowmax<false>(sr, 0, 0, tile_max);
+            if (need_mask) chunk_softmax<true, true>(sr, c2, mb, lo0 - c * 32, hi0 - c * 32, pk, psum, tile_max);
+            else chunk_softmax<false, true>(sr, c2, mb, 0, 0, pk, psum, tile_max);
+            if (!pv_waited) {  // P_w's shared memory is still being read by the previous tile's P.V until this fires
+              mbar_wait(bPVdone(w), (i - 1) & 1);
+              pv_waited = true;
             }
             const uint32_t prow = sPw + (c >> 1) * kTileBytes + r * 128;
 #pragma unroll
@@ -395,59 +385,61 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
               st_shared_v4(prow + ((cc ^ (r & 7)) << 4), make_uint4(pk[v * 4], pk[v * 4 + 1], pk[v * 4 + 2], pk[v * 4 + 3]));
             }
           }
-          if (exact) break;
-          const bool bad = !((tile_max - ref_new) * c2 <= 60.f);  // also true for ref = -inf / NaN
+          if (!check) break;
+          const bool bad = !((tile_max - ref) * c2 <= 60.f);
           if (!__any_sync(0xffffffffu, bad)) break;
-          ref_new = fmaxf(m_seen, tile_max);
-          exact = true;
+          // a score beyond 2^60 of the reference: move the reference, rescale what has been accumulated, redo the tile
+          const float ref_new = fmaxf(ref, tile_max);
+          const float alpha = ex2f((ref - ref_new) * c2);
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t orr[16];
+            tmem_ld_32x32b_x16(tO + c * 16, orr);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 16; ++k) orr[k] = __float_as_uint(__uint_as_float(orr[k]) * alpha);
+            tmem_st_32x32b_x16(tO + c * 16, orr);
+          }
+          tmem_st_wait();
+          l_run *= alpha;
+          ref = ref_new;
+          check = false;
         }
-        m_seen = exact ? ref_new : fmaxf(m_seen, tile_max);
-        ref = ref_new;
-        l_run = l_run * alpha + psum;
+        l_run += psum.x + psum.y;
         tc_fence_before();
         fence_proxy_async_smem();
         mbar_arrive(bPfull(w));
         TRACE(w * 2 + 0, i * 4 + 3);
-        // ---- fold the previous tile's P.V (already complete: its MMAs precede S_i in the tensor pipe)
-        if (i > 0) {
-          const int ob = (i - 1) & 1;
-          mbar_wait(bOfull(w, ob), ((i - 1) >> 1) & 1);
-          tc_fence_after();
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            uint32_t orr[32];
-            tmem_ld_32x32b_x32(tO + ob * 64 + c * 32, orr);
-            tmem_ld_wait();
-#pragma unroll
-            for (int k = 0; k < 32; ++k) acc[c * 32 + k] = fmaf(acc[c * 32 + k], alpha_prev, __uint_as_float(orr[k]));
-          }
-        }
-        alpha_prev = alpha;
       }
-      // ---- epilogue: last tile's P.V, normalise, store
+      // ---- epilogue: O is complete in TMEM; normalise, store
       {
-        const int ob = (n_it - 1) & 1;
-        mbar_wait(bOfull(w, ob), ((n_it - 1) >> 1) & 1);
+        mbar_wait(bPVdone(w), (n_it - 1) & 1);
         tc_fence_after();
         const float inv_l = 1.f / l_run;
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t orr[32];
-          tmem_ld_32x32b_x32(tO + ob * 64 + c * 32, orr);
-          tmem_ld_wait();
-#pragma unroll
-          for (int k = 0; k < 32; ++k) acc[c * 32 + k] = fmaf(acc[c * 32 + k], alpha_prev, __uint_as_float(orr[k])) * inv_l;
-        }
+        uint32_t o0[32], o1[32];
+        tmem_ld_32x32b_x32(tO, o0);
+        tmem_ld_32x32b_x32(tO + 32, o1);
+        tmem_ld_wait();
         if (t < T) {
           __nv_bfloat16* orow = out + (seq_row0 + t) * d + h * 64;
 #pragma unroll
-          for (int v = 0; v < 8; ++v) {
+          for (int v = 0; v < 4; ++v) {
             uint4 o;
-            o.x = pack_bf16x2(acc[v * 8 + 0], acc[v * 8 + 1]);
-            o.y = pack_bf16x2(acc[v * 8 + 2], acc[v * 8 + 3]);
-            o.z = pack_bf16x2(acc[v * 8 + 4], acc[v * 8 + 5]);
-            o.w = pack_bf16x2(acc[v * 8 + 6], acc[v * 8 + 7]);
+            o.x = pack_bf16x2(__uint_as_float(o0[v * 8 + 0]) * inv_l, __uint_as_float(o0[v * 8 + 1]) * inv_l);
+            o.y = pack_bf16x2(__uint_as_float(o0[v * 8 + 2]) * inv_l, __uint_as_float(o0[v * 8 + 3]) * inv_l);
+            o.z = pack_bf16x2(__uint_as_float(o0[v * 8 + 4]) * inv_l, __uint_as_float(o0[v * 8 + 5]) * inv_l);
+            o.w = pack_bf16x2(__uint_as_float(o0[v * 8 + 6]) * inv_l, __uint_as_float(o0[v * 8 + 7]) * inv_l);
             *reinterpret_cast<uint4*>(orow + v * 8) = o;
+          }
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            uint4 o;
+            o.x = pack_bf16x2(__uint_as_float(o1[v * 8 + 0]) * inv_l, __uint_as_float(o1[v * 8 + 1]) * inv_l);
+            o.y = pack_bf16x2(__uint_as_float(o1[v * 8 + 2]) * inv_l, __uint_as_float(o1[v * 8 + 3]) * inv_l);
+            o.z = pack_bf16x2(__uint_as_float(o1[v * 8 + 4]) * inv_l, __uint_as_float(o1[v * 8 + 5]) * inv_l);
+            o.w = pack_bf16x2(__uint_as_float(o1[v * 8 + 6]) * inv_l, __uint_as_float(o1[v * 8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + 32 + v * 8) = o;
           }
           lse[(static_cast<long>(b) * NH + h) * T + t] = ref * kSoftmaxScale + logf(l_run);
         }
@@ -456,7 +448,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __nv_bfloat16*
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 11) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
@@ -505,7 +497,7 @@ struct AttnBwdSmem {
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                const __grid_constant__ CUtensorMap tm_dq, const __nv_bfloat16* __restrict__ qkv, const float* __restrict__ cos_sin,
+                const __grid_constant__ CUtensorMap tm_dq, const float* __restrict__ cos_sin,
                 const int32_t* __restrict__ doc_start, const float* __restrict__ lse, const float* __restrict__ delta,
                 float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
@@ -513,10 +505,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV, sQ = sbase + AttnBwdSmem::kQ,
                  sdO = sbase + AttnBwdSmem::kdO, sP = sbase + AttnBwdSmem::kP, sdS = sbase + AttnBwdSmem::kdS,
                  sBar = sbase + AttnBwdSmem::kBar;
-  const uint32_t bKready = sBar;                                // (128)
-  const uint32_t bVfull = sBar + 8;                             // (tx)
-  auto bQready = [&](int s) { return sBar + 8u * (2 + s); };    // [2] (128)
-  auto bdOfull = [&](int s) { return sBar + 8u * (4 + s); };    // [2] (tx)
+  const uint32_t bKVfull = sBar;                                // (tx: K and V)
+  auto bQdOfull = [&](int s) { return sBar + 8u * (2 + s); };   // [2] (tx: Q_i and dO_i)
   auto bStageEmpty = [&](int s) { return sBar + 8u * (6 + s); };  // [2] (1, commit)
   const uint32_t bSdPfull = sBar + 8u * 8;                      // (1, commit)
   const uint32_t bPdSfull = sBar + 8u * 9;                      // (256)
@@ -528,7 +518,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef PCV_TRACE
-  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 384);
+  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 288);
 #endif
   const int j = blockIdx.x;  // key tile
   const int h = blockIdx.y, b = blockIdx.z;
@@ -551,15 +541,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
   const int n_it = i_hi - i_lo + 1;
 
-  if (warp == 12 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     tma_prefetch_desc(&tm_dq);
-    mbar_init(bKready, 128);
-    mbar_init(bVfull, 1);
+    mbar_init(bKVfull, 1);
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bQready(s), 128);
-      mbar_init(bdOfull(s), 1);
+      mbar_init(bQdOfull(s), 1);
       mbar_init(bStageEmpty(s), 1);
     }
     mbar_init(bSdPfull, 1);
@@ -569,43 +557,37 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(bAccFull, 1);
     fence_mbar_init();
   }
-  if (warp == 11) tmem_alloc<512>(tmem_ptr_smem);
+  if (warp == 8) tmem_alloc<512>(tmem_ptr_smem);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
   const uint32_t tS = tmem_base, tdP = tmem_base + 128, tdV = tmem_base + 256, tdK = tmem_base + 320, tdQ = tmem_base + 384;
 
-  if (warp >= 8 && warp < 12) {
-    // ============================== loader warps ==============================
-    const int ltid = tid - 256;
-    if (ltid == 0) {
-      mbar_expect_tx(bVfull, kTileBytes);
-      tma_load_2d(sV, &tm_qkv, bVfull, 2 * d + h * 64, static_cast<int>(seq_row0) + key0);
-    }
-    load_rope_tile(sK, qkv + d + h * 64, ld, seq_row0 + key0, key0, T, cos_sin, ltid);
-    fence_proxy_async_smem();
-    mbar_arrive(bKready);
-    for (int it = 0; it < n_it; ++it) {
-      const int i = i_lo + it;
-      const int stage = it & 1;
-      mbar_wait(bStageEmpty(stage), ((it >> 1) & 1) ^ 1u);
-      if (ltid == 0) {
-        mbar_expect_tx(bdOfull(stage), kTileBytes);
-        tma_load_2d(sdO + stage * kTileBytes, &tm_do, bdOfull(stage), h * 64, static_cast<int>(seq_row0) + i * 128);
+  if (warp == 8) {
+    // ============================== TMA producer (q, k in qkv are already rotated) ==============================
+    if (lane == 0) {
+      const int row0 = static_cast<int>(seq_row0);
+      mbar_expect_tx(bKVfull, 2 * kTileBytes);
+      tma_load_2d(sK, &tm_qkv, bKVfull, d + h * 64, row0 + key0);
+      tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + h * 64, row0 + key0);
+      for (int it = 0; it < n_it; ++it) {
+        const int i = i_lo + it;
+        const int stage = it & 1;
+        mbar_wait(bStageEmpty(stage), ((it >> 1) & 1) ^ 1u);
+        mbar_expect_tx(bQdOfull(stage), 2 * kTileBytes);
+        tma_load_2d(sQ + stage * kTileBytes, &tm_qkv, bQdOfull(stage), h * 64, row0 + i * 128);
+        tma_load_2d(sdO + stage * kTileBytes, &tm_do, bQdOfull(stage), h * 64, row0 + i * 128);
       }
-      load_rope_tile(sQ + stage * kTileBytes, qkv + h * 64, ld, seq_row0 + i * 128, i * 128, T, cos_sin, ltid);
-      fence_proxy_async_smem();
-      mbar_arrive(bQready(stage));
     }
-  } else if (warp == 12) {
+    __syncwarp();
+  } else if (warp == 9) {
     // ============================== MMA issuer ==============================
     if (lane == 0) {
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);   // S, dP
       constexpr uint32_t idesc_kv = umma_idesc_bf16(128, 64, true, true);     // dV = P^T.dO, dK = dS^T.Q
       constexpr uint32_t idesc_dq = umma_idesc_bf16(128, 64, false, true);    // dQ = dS.K
-      mbar_wait(bKready, 0);
-      mbar_wait(bVfull, 0);
+      mbar_wait(bKVfull, 0);
       tc_fence_after();
       auto issue_SdP = [&](int stage) {
 #pragma unroll
@@ -623,8 +605,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tc_commit(bSdPfull);
       };
       if (n_it > 0) {
-        mbar_wait(bQready(0), 0);
-        mbar_wait(bdOfull(0), 0);
+        mbar_wait(bQdOfull(0), 0);
         tc_fence_after();
         issue_SdP(0);
       }
@@ -638,8 +619,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         // next tile's S and dP first: they are what the compute warps wait for
         if (it + 1 < n_it) {
           const int s1 = (it + 1) & 1;
-          mbar_wait(bQready(s1), ((it + 1) >> 1) & 1);
-          mbar_wait(bdOfull(s1), ((it + 1) >> 1) & 1);
+          mbar_wait(bQdOfull(s1), ((it + 1) >> 1) & 1);
           tc_fence_after();
           issue_SdP(s1);
         }
@@ -790,7 +770,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 11) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
@@ -820,6 +800,24 @@ __global__ void attn_bwd_dq_post_kernel(const float* __restrict__ dq_acc, const 
   }
 }
 
+
+// In-place interleaved-pair RoPE of the q and k columns of qkv[B*T][3d] (models/LM/embedding.py:28-67); the model
+// path fuses this into the QKV GEMM epilogue instead (pcv_gemm_bf16_rope).
+__global__ void rope_qk_kernel(__nv_bfloat16* __restrict__ qkv, const float* __restrict__ cos_sin, long BT, int T, int d) {
+  const int vpr = 2 * d / 8;  // 16-byte chunks in the q|k part of a row
+  const long total = BT * vpr;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const long row = i / vpr;
+    const int col = static_cast<int>(i % vpr) * 8;
+    const int t = static_cast<int>(row % T);
+    const int fc = (col & 63) >> 1;
+    uint4* ptr = reinterpret_cast<uint4*>(qkv + row * 3 * d + col);
+    const float4* cs = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(t) * 32 + fc) * 2);
+    *ptr = rope_chunk(*ptr, __ldg(cs), __ldg(cs + 1), 1.f);
+  }
+}
+
 }  // namespace pcv
 
 using namespace pcv;
@@ -836,9 +834,25 @@ extern "C" int pcv_debug_read_trace(long long* host, int n) {
 }
 #endif
 
-extern "C" int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, void* out, float* lse,
-                            int B, int T, int n_heads, void* stream) {
-  if (!qkv || !cos_sin || !out || !lse) return PCV_ERR_ARG;
+extern "C" int pcv_rope_qk(void* qkv, const float* cos_sin, int B, int T, int n_heads, void* stream) {
+  if (!qkv || !cos_sin) return PCV_ERR_ARG;
+  int rc = attn_check(B, T, n_heads);
+  if (rc) return rc;
+  const int d = n_heads * 64;
+  const long BT = static_cast<long>(B) * T;
+  const long total = BT * (2 * d / 8);
+  long blocks = (total + 255) / 256;
+  const long cap = static_cast<long>(num_sms()) * 16;
+  if (blocks > cap) blocks = cap;
+  rope_qk_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<__nv_bfloat16*>(qkv), cos_sin, BT, T, d);
+  count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_attn_fwd(const void* qkv, const int32_t* doc_start, void* out, float* lse, int B, int T, int n_heads,
+                            void* stream) {
+  if (!qkv || !out || !lse) return PCV_ERR_ARG;
   int rc = attn_check(B, T, n_heads);
   if (rc) return rc;
   const int d = n_heads * 64;
@@ -853,7 +867,7 @@ extern "C" int pcv_attn_fwd(const void* qkv, const float* cos_sin, const int32_t
   }
   dim3 grid((T + 255) / 256, n_heads, B);
   attn_fwd_kernel<<<grid, kAttnThreads, AttnFwdSmem::kBytes, static_cast<cudaStream_t>(stream)>>>(
-      tm, static_cast<const __nv_bfloat16*>(qkv), cos_sin, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
+      tm, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
   count_launch();
   return cuda_rc();
 }
@@ -890,7 +904,7 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   }
   dim3 grid(T / 128, n_heads, B);
   attn_bwd_kernel<<<grid, kAttnThreads, AttnBwdSmem::kBytes, st>>>(
-      tm_qkv, tm_do, tm_dq, static_cast<const __nv_bfloat16*>(qkv), cos_sin, doc_start, lse, delta, dq_acc,
+      tm_qkv, tm_do, tm_dq, cos_sin, doc_start, lse, delta, dq_acc,
       static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
   {
     const long total = BT * (d / 8);

@@ -48,7 +48,11 @@ struct GemmParams {
   int ldc;
   int m_tiles, n_tiles, splits, kb_per_split, kb_total;
   float alpha;
+  // EPI_BF16_ROPE only: interleaved-pair rotation of output columns [0, rope_cols) at position (row % T)
+  const float* cos_sin;
+  int T, rope_cols;
 };
+constexpr int EPI_BF16_ROPE = 3;  // internal: PCV_EPI_BF16 + RoPE (pcv_gemm_bf16_rope)
 
 // Work item -> (m tile, n tile, k split).  Tiles are visited in column-major order inside groups of kGroupM tile
 // rows, so the CTAs that run concurrently share a few A tiles AND a few B tiles (L2 reuse for wide outputs such as
@@ -71,7 +75,35 @@ __device__ __forceinline__ void decode_work(const GemmParams& p, int w, int& m_b
 // One thread's 32 consecutive accumulator columns of one output row -> global memory.
 template <int EPI>
 __device__ __forceinline__ void store_row_chunk(const GemmParams& p, int row, int col0, const uint32_t* r) {
-  if constexpr (EPI == PCV_EPI_BF16) {
+  if constexpr (EPI == EPI_BF16_ROPE) {
+    // q and k columns: rotate the 16 (even, odd) pairs of this chunk in fp32, before the bf16 rounding
+    // (apply_rotary_emb_complex_like, models/LM/embedding.py:28-67); v columns pass through.
+    __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
+    const bool rot = col0 < p.rope_cols;
+    const float4* cs = reinterpret_cast<const float4*>(p.cos_sin + (static_cast<size_t>(row % p.T) * 32 + ((col0 & 63) >> 1)) * 2);
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      if (col0 + v * 8 + 8 <= p.N) {
+        float x[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = __uint_as_float(r[v * 8 + k]) * p.alpha;
+        if (rot) {
+          const float4 c0 = __ldg(cs + 2 * v), c1 = __ldg(cs + 2 * v + 1);  // (cos, sin) x 2 pairs each
+          const float a0 = x[0], b0 = x[1], a1 = x[2], b1 = x[3], a2 = x[4], b2 = x[5], a3 = x[6], b3 = x[7];
+          x[0] = a0 * c0.x - b0 * c0.y; x[1] = b0 * c0.x + a0 * c0.y;
+          x[2] = a1 * c0.z - b1 * c0.w; x[3] = b1 * c0.z + a1 * c0.w;
+          x[4] = a2 * c1.x - b2 * c1.y; x[5] = b2 * c1.x + a2 * c1.y;
+          x[6] = a3 * c1.z - b3 * c1.w; x[7] = b3 * c1.z + a3 * c1.w;
+        }
+        uint4 o;
+        o.x = pack_bf16x2(x[0], x[1]);
+        o.y = pack_bf16x2(x[2], x[3]);
+        o.z = pack_bf16x2(x[4], x[5]);
+        o.w = pack_bf16x2(x[6], x[7]);
+        *reinterpret_cast<uint4*>(crow + v * 8) = o;
+      }
+    }
+  } else if constexpr (EPI == PCV_EPI_BF16) {
     __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + static_cast<size_t>(row) * p.ldc + col0;
 #pragma unroll
     for (int v = 0; v < 4; ++v) {
@@ -557,6 +589,9 @@ static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, c
     case PCV_EPI_BF16: return launch_gemm<BN, A_MN, B_MN, PCV_EPI_BF16>(ta, tb, p, grid, st);
     case PCV_EPI_F32_ATOMIC: return launch_gemm<BN, A_MN, B_MN, PCV_EPI_F32_ATOMIC>(ta, tb, p, grid, st);
     case PCV_EPI_F32: return launch_gemm<BN, A_MN, B_MN, PCV_EPI_F32>(ta, tb, p, grid, st);
+    case EPI_BF16_ROPE:
+      if constexpr (!A_MN && B_MN) return launch_gemm<BN, A_MN, B_MN, EPI_BF16_ROPE>(ta, tb, p, grid, st);
+      else return PCV_ERR_ARG;
   }
   return PCV_ERR_ARG;
 }
@@ -593,6 +628,9 @@ static int dispatch_epi_pair(int epi, const CUtensorMap& ta, const CUtensorMap& 
     case PCV_EPI_BF16: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_BF16>(ta, tb, p, grid, st);
     case PCV_EPI_F32_ATOMIC: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32_ATOMIC>(ta, tb, p, grid, st);
     case PCV_EPI_F32: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32>(ta, tb, p, grid, st);
+    case EPI_BF16_ROPE:
+      if constexpr (!A_MN && B_MN) return launch_gemm_pair<A_MN, B_MN, EPI_BF16_ROPE>(ta, tb, p, grid, st);
+      else return PCV_ERR_ARG;
   }
   return PCV_ERR_ARG;
 }
@@ -634,14 +672,15 @@ extern "C" int pcv_gemm_set_mode(int mode) {
   return PCV_OK;
 }
 
-extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
-                             int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream) {
+static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                     int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, const float* cos_sin, int T,
+                     int rope_cols, void* stream) {
   using namespace pcv;
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return PCV_ERR_ARG;
   if (splits < 0) return PCV_ERR_ARG;
   if (splits == 0) splits = (epilogue == PCV_EPI_F32_ATOMIC) ? auto_splits(M, N, K) : 1;
   if (epilogue != PCV_EPI_F32_ATOMIC && splits != 1) return PCV_ERR_ARG;
-  const int vec = (epilogue == PCV_EPI_BF16) ? 8 : 4;
+  const int vec = (epilogue == PCV_EPI_BF16 || epilogue == EPI_BF16_ROPE) ? 8 : 4;
   if (N % vec || ldc % vec || (reinterpret_cast<uintptr_t>(C) & 15)) return PCV_ERR_ALIGN;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -668,6 +707,7 @@ extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N
       p.m_tiles = m2; p.n_tiles = n2;
       p.kb_total = kb_total; p.kb_per_split = kps; p.splits = sp;
       p.alpha = alpha;
+      p.cos_sin = cos_sin; p.T = T; p.rope_cols = rope_cols;
       const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
       count_launch();
       return dispatch_major_pair(a_mn_major, b_mn_major, epilogue, ta, tb, p, static_cast<int>(2 * pairs), st);
@@ -699,9 +739,22 @@ extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.alpha = alpha;
+  p.cos_sin = cos_sin; p.T = T; p.rope_cols = rope_cols;
   const long total = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
   count_launch();
   if (BN == 256) return dispatch_major<256>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
   return dispatch_major<128>(a_mn_major, b_mn_major, epilogue, ta, tb, p, grid, st);
+}
+
+extern "C" int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                             int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream) {
+  if (epilogue < PCV_EPI_BF16 || epilogue > PCV_EPI_F32) return PCV_ERR_ARG;
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, epilogue, splits, alpha, nullptr, 1, 0, stream);
+}
+
+extern "C" int pcv_gemm_bf16_rope(const void* X, const void* W, void* Y, int M, int N, int K, int ldx, int ldw, int ldy,
+                                  const float* cos_sin, int T, int rope_cols, void* stream) {
+  if (!cos_sin || T <= 0 || rope_cols < 0 || rope_cols > N || rope_cols % 64 || M % T) return PCV_ERR_ARG;
+  return gemm_impl(X, W, Y, M, N, K, ldx, ldw, ldy, 0, 1, pcv::EPI_BF16_ROPE, 1, 1.0f, cos_sin, T, rope_cols, stream);
 }

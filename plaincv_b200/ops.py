@@ -52,6 +52,22 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def linear_fwd_rope(x: torch.Tensor, w: torch.Tensor, cos_sin: torch.Tensor, T: int, rope_cols: int) -> torch.Tensor:
+    """qkv[M,3d] = rope(x @ w_qkv): the QKV projection with RoPE applied to the q | k columns in the GEMM epilogue."""
+    M, K = x.shape
+    Np = w.shape[1]
+    y = torch.empty((M, Np), dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().pcv_gemm_bf16_rope(x.data_ptr(), w.data_ptr(), y.data_ptr(), M, Np, K, K, Np, Np,
+                                         cos_sin.data_ptr(), T, rope_cols, _stream()), "pcv_gemm_bf16_rope")
+    return y
+
+
+def rope_qk_(qkv: torch.Tensor, cos_sin: torch.Tensor, B: int, T: int, n_heads: int) -> torch.Tensor:
+    """In-place RoPE of the q | k columns of qkv (stand-alone form of the fused epilogue above)."""
+    check(_lib.load().pcv_rope_qk(qkv.data_ptr(), cos_sin.data_ptr(), B, T, n_heads, _stream()), "pcv_rope_qk")
+    return qkv
+
+
 def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, alpha: float = 1.0) -> torch.Tensor:
     """dx[M,K] = dy[M,Np] @ w[K,Np]^T."""
     M, Np = dy.shape
@@ -124,18 +140,20 @@ def swiglu_bwd(gu: torch.Tensor, dh: torch.Tensor) -> torch.Tensor:
     return dgu
 
 
-def attn_fwd(qkv: torch.Tensor, cos_sin: torch.Tensor, doc_start: Optional[torch.Tensor], B: int, T: int,
+def attn_fwd(qkv: torch.Tensor, doc_start: Optional[torch.Tensor], B: int, T: int,
              n_heads: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """qkv: q and k columns already rotated (linear_fwd_rope / rope_qk_)."""
     d = n_heads * 64
     out = torch.empty((B * T, d), dtype=torch.bfloat16, device=qkv.device)
     lse = torch.empty((B, n_heads, T), dtype=torch.float32, device=qkv.device)
-    check(_lib.load().pcv_attn_fwd(qkv.data_ptr(), cos_sin.data_ptr(), _p(doc_start), out.data_ptr(), lse.data_ptr(),
+    check(_lib.load().pcv_attn_fwd(qkv.data_ptr(), _p(doc_start), out.data_ptr(), lse.data_ptr(),
                                    B, T, n_heads, _stream()), "pcv_attn_fwd")
     return out, lse
 
 
 def attn_bwd(qkv: torch.Tensor, cos_sin: torch.Tensor, doc_start: Optional[torch.Tensor], out: torch.Tensor,
              dout: torch.Tensor, lse: torch.Tensor, B: int, T: int, n_heads: int) -> torch.Tensor:
+    """qkv: rotated (as given to attn_fwd); returns the gradient w.r.t. the un-rotated qkv."""
     d = n_heads * 64
     dqkv = torch.empty_like(qkv)
     delta = torch.empty((B, n_heads, T), dtype=torch.float32, device=qkv.device)
@@ -241,7 +259,8 @@ class SwiGLUFn(torch.autograd.Function):
 class AttentionFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv, cos_sin, doc_start, B, T, n_heads):
-        out, lse = attn_fwd(qkv, cos_sin, doc_start, B, T, n_heads)
+        qkv = rope_qk_(qkv.clone(), cos_sin, B, T, n_heads)  # un-fused form; BlockFn fuses RoPE into the QKV GEMM
+        out, lse = attn_fwd(qkv, doc_start, B, T, n_heads)
         ctx.save_for_backward(qkv, out, lse, cos_sin, doc_start if doc_start is not None else torch.empty(0))
         ctx.has_doc = doc_start is not None
         ctx.dims = (B, T, n_heads)
@@ -285,8 +304,8 @@ class BlockFn(torch.autograd.Function):
     def forward(ctx, res, delta, layer, rt):
         eps = rt.eps
         res1, h1, rstd1 = rmsnorm_residual_fwd(res, delta, layer.attn_norm, eps)
-        qkv = linear_fwd(h1, layer.w_qkv)
-        o, lse = attn_fwd(qkv, rt.cos_sin, rt.doc_start, rt.B, rt.T, rt.n_heads)
+        qkv = linear_fwd_rope(h1, layer.w_qkv, rt.cos_sin, rt.T, 2 * rt.n_heads * 64)  # q, k stored rotated
+        o, lse = attn_fwd(qkv, rt.doc_start, rt.B, rt.T, rt.n_heads)
         a = linear_fwd(o, layer.w_out)
         res2, h2, rstd2 = rmsnorm_residual_fwd(res1, a, layer.mlp_norm, eps)
         del a

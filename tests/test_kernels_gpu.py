@@ -148,17 +148,38 @@ def test_attention_fwd_bwd(ops, B, T, NH, doc_mean):
     doc_start = _doc_starts(B, T, 11, doc_mean) if doc_mean else None
     cos_sin = ops.rope_table(64, T, theta, "cuda")
     ds_dev = None if doc_start is None else doc_start.to(torch.int32).cuda().view(-1)
-    out, lse = ops.attn_fwd(qkv.cuda(), cos_sin, ds_dev, B, T, NH)
+    qkv_rot = ops.rope_qk_(qkv.cuda().clone(), cos_sin, B, T, NH)  # stand-alone form of the fused GEMM epilogue
+    out, lse = ops.attn_fwd(qkv_rot, ds_dev, B, T, NH)
     torch.cuda.synchronize()
     qkv32 = qkv.float().requires_grad_(True)
     ref = _attention_oracle(qkv32, B, T, NH, theta, doc_start)
     assert rel_l2(out, ref) < 1e-2, "attention forward"
     ref.backward(dout.float())
-    dqkv = ops.attn_bwd(qkv.cuda(), cos_sin, ds_dev, out, dout.cuda(), lse, B, T, NH)
+    dqkv = ops.attn_bwd(qkv_rot, cos_sin, ds_dev, out, dout.cuda(), lse, B, T, NH)
     torch.cuda.synchronize()
     gref = qkv32.grad
     for name, sl in (("dq", slice(0, d)), ("dk", slice(d, 2 * d)), ("dv", slice(2 * d, 3 * d))):
         assert rel_l2(dqkv[:, sl], gref[:, sl]) < 1.5e-2, f"attention backward {name}"
+
+
+def test_fused_rope_gemm_matches_gemm_then_rope(ops):
+    """pcv_gemm_bf16_rope == RoPE(fp32 x@w) on the q|k columns, plain GEMM on the v columns (embedding.py:28-67)."""
+    g = torch.Generator().manual_seed(12)
+    B, T, NH = 2, 256, 4
+    d = NH * 64
+    x = _bf(torch.randn(B * T, d, generator=g))
+    w = _bf(torch.randn(d, 3 * d, generator=g) * 0.05)
+    cos_sin = ops.rope_table(64, T, 500000.0, "cuda")
+    y = ops.linear_fwd_rope(x.cuda(), w.cuda(), cos_sin, T, 2 * d)
+    y32 = (x.float() @ w.float()).view(B, T, 3 * d)
+    q, k, v = torch.split(y32, d, dim=-1)
+    freqs = O.precompute_freqs_cis(64, T, 500000.0)
+    qr, kr = O.apply_rotary_emb_complex_like(q.reshape(B, T, NH, 64), k.reshape(B, T, NH, 64), freqs)
+    ref = torch.cat([qr.reshape(B, T, d), kr.reshape(B, T, d), v], dim=-1).view(B * T, 3 * d)
+    assert rel_l2(y, ref) < 5e-3
+    # and the stand-alone rotation agrees with the fused one up to the extra bf16 rounding
+    y2 = ops.rope_qk_(ops.linear_fwd(x.cuda(), w.cuda()), cos_sin, B, T, NH)
+    assert rel_l2(y2, ref) < 8e-3
 
 
 def test_attention_first_row_is_v0(ops):
@@ -169,7 +190,7 @@ def test_attention_first_row_is_v0(ops):
     qkv = _bf(torch.randn(B * T, 3 * d, generator=g))
     cos_sin = ops.rope_table(64, T, 500000.0, "cuda")
     ds = torch.arange(T, dtype=torch.int32).cuda()  # every token its own document
-    out, _ = ops.attn_fwd(qkv.cuda(), cos_sin, ds, B, T, NH)
+    out, _ = ops.attn_fwd(ops.rope_qk_(qkv.cuda().clone(), cos_sin, B, T, NH), ds, B, T, NH)
     assert torch.equal(out.cpu(), qkv[:, 2 * d:])  # each row returns exactly its own v
 
 

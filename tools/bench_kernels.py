@@ -40,10 +40,10 @@ def timeit(fn, iters=int(os.environ.get('PCV_KB_ITERS', 10)), warm=int(os.enviro
 if which in ("all", "attn"):
     qkv = torch.randn(M, 3 * d, device=dev).to(bf)
     cos_sin = ops.rope_table(64, T, 500000.0, dev)
-    out, lse = ops.attn_fwd(qkv, cos_sin, None, B, T, NH)
+    out, lse = ops.attn_fwd(qkv, None, B, T, NH)
     dout = torch.randn(M, d, device=dev).to(bf)
     fl_fwd = 4.0 * B * NH * T * T * 64 / 2
-    ms = timeit(lambda: ops.attn_fwd(qkv, cos_sin, None, B, T, NH))
+    ms = timeit(lambda: ops.attn_fwd(qkv, None, B, T, NH))
     res["attn_fwd"] = (ms, fl_fwd / ms / 1e9, "TFLOP/s (causal-half flops)")
     ms = timeit(lambda: ops.attn_bwd(qkv, cos_sin, None, out, dout, lse, B, T, NH))
     res["attn_bwd"] = (ms, 2.5 * fl_fwd / ms / 1e9, "TFLOP/s (5 GEMMs, causal-half)")
@@ -56,7 +56,7 @@ if which in ("all", "attn"):
             ds[b, t:t + n] = t
             t += n
     ds = ds.to(dev).view(-1)
-    ms = timeit(lambda: ops.attn_fwd(qkv, cos_sin, ds, B, T, NH))
+    ms = timeit(lambda: ops.attn_fwd(qkv, ds, B, T, NH))
     res["attn_fwd_doc512"] = (ms, 0, "")
     ms = timeit(lambda: ops.attn_bwd(qkv, cos_sin, ds, out, dout, lse, B, T, NH))
     res["attn_bwd_doc512"] = (ms, 0, "")
@@ -98,6 +98,11 @@ if which in ("all", "gemm"):
         res[f"gemm_wgrad_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
 
     gemm_set("qkv", d, 3 * d)
+    xx = torch.randn(M, d, device=dev).to(bf)
+    wq = (torch.randn(d, 3 * d, device=dev) * 0.02).to(bf)
+    cs_t = ops.rope_table(64, T, 500000.0, dev)
+    ms = timeit(lambda: ops.linear_fwd_rope(xx, wq, cs_t, T, 2 * d))
+    res["gemm_fwd_qkv+rope"] = (ms, 2.0 * M * d * 3 * d / ms / 1e9, "TFLOP/s")
     gemm_set("out", d, d)
     gemm_set("gu", d, 2 * hp)
     gemm_set("down", hp, d)

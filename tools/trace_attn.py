@@ -12,7 +12,7 @@ d = NH * 64
 qkv = torch.randn(B * T, 3 * d, device="cuda").to(torch.bfloat16)
 cs = ops.rope_table(64, T, 500000.0, "cuda")
 for _ in range(3):
-    out, lse = ops.attn_fwd(qkv, cs, None, B, T, NH)
+    out, lse = ops.attn_fwd(qkv, None, B, T, NH)
 torch.cuda.synchronize()
 lib = _lib.load()
 buf = (ctypes.c_longlong * 8192)()
