@@ -24,7 +24,7 @@
 // Backward CTA (416 threads) = one (batch, head, 128-key tile), looping over the query tiles that can see it:
 //   S = Q_i.K^T, dP = dO_i.V^T  ->  P = exp2(S*c - lse), dS = P*(dP - delta)*scale (256 threads, half a row each)
 //   dV += P^T.dO_i, dK += dS^T.Q_i (accumulated in TMEM over the loop), dQ_i = dS.K (read back, red.add into fp32 dq)
-// TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448).
+// TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448) dS(bf16 pairs) [448,512).
 #include "sm100.cuh"
 #include "pcv_internal.h"
 #include <math.h>
@@ -39,7 +39,8 @@ __device__ long long g_trace[8192];
 #define TRACE(slot, idx) do { } while (0)
 #endif
 
-constexpr int kAttnThreads = 320;
+constexpr int kAttnThreads = 320;     // forward
+constexpr int kAttnBwdThreads = 512;  // backward: 2 compute warpgroups, 1 dQ warpgroup, producer + MMA warps
 constexpr int kTileBytes = 128 * 128;  // 128 rows x 64 bf16
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kSoftmaxScale = 0.125f;  // 1/sqrt(64)
@@ -104,22 +105,24 @@ __device__ __forceinline__ float chunk_exp_pack(const uint32_t* sr, float c2, fl
   return s0 + s1;
 }
 
-// backward: p = exp2(s*c2 - lse2), ds = p * (dp*scale - delta*scale), both packed to bf16 pairs
+// backward: p = exp2(s*c2 - lse2), ds = p * (dp*scale - delta*scale), both packed to bf16 pairs (fp32x2 math)
 template <bool MASK>
 __device__ __forceinline__ void chunk_p_ds(const uint32_t* sr, const uint32_t* pr, float c2, float lse2, float dlt_s,
                                            int lo, int hi, uint32_t* pk_p, uint32_t* pk_ds) {
+  const float2 c2v = make_float2(c2, c2), lv = make_float2(-lse2, -lse2);
+  const float2 scv = make_float2(kSoftmaxScale, kSoftmaxScale), dv = make_float2(-dlt_s, -dlt_s);
 #pragma unroll
   for (int k = 0; k < 32; k += 2) {
-    float e0 = ex2f(fmaf(__uint_as_float(sr[k]), c2, -lse2));
-    float e1 = ex2f(fmaf(__uint_as_float(sr[k + 1]), c2, -lse2));
+    const float2 x = __ffma2_rn(make_float2(__uint_as_float(sr[k]), __uint_as_float(sr[k + 1])), c2v, lv);
+    float2 e = make_float2(ex2f(x.x), ex2f(x.y));
     if (MASK) {
-      e0 = (k >= lo && k <= hi) ? e0 : 0.f;
-      e1 = (k + 1 >= lo && k + 1 <= hi) ? e1 : 0.f;
+      e.x = (k >= lo && k <= hi) ? e.x : 0.f;
+      e.y = (k + 1 >= lo && k + 1 <= hi) ? e.y : 0.f;
     }
-    const float g0 = e0 * fmaf(__uint_as_float(pr[k]), kSoftmaxScale, -dlt_s);
-    const float g1 = e1 * fmaf(__uint_as_float(pr[k + 1]), kSoftmaxScale, -dlt_s);
-    pk_p[k >> 1] = pack_bf16x2(e0, e1);
-    pk_ds[k >> 1] = pack_bf16x2(g0, g1);
+    const float2 tt = __ffma2_rn(make_float2(__uint_as_float(pr[k]), __uint_as_float(pr[k + 1])), scv, dv);
+    const float2 g = __fmul2_rn(e, tt);
+    pk_p[k >> 1] = pack_bf16x2(e.x, e.y);
+    pk_ds[k >> 1] = pack_bf16x2(g.x, g.y);
   }
 }
 
@@ -128,8 +131,7 @@ struct AttnFwdSmem {
   static constexpr int kQ = 0;                          // 2 tiles
   static constexpr int kK = kQ + 2 * kTileBytes;        // 3 slots
   static constexpr int kV = kK + 3 * kTileBytes;        // 3 slots
-  static constexpr int kP = kV + 3 * kTileBytes;        // 2 x (128 x 128 bf16)
-  static constexpr int kBar = kP + 2 * 2 * kTileBytes;  // barriers
+  static constexpr int kBar = kV + 3 * kTileBytes;      // barriers
   static constexpr int kBytes = kBar + 256 + 1024;
 };
 
@@ -166,14 +168,14 @@ __device__ __forceinline__ void chunk_softmax(const uint32_t* sr, float c2, floa
 //                     precision), so P.V accumulates in TMEM across key tiles with no per-tile rescale or read-back.
 //   warp 8          : TMA producer (Q once, K / V ring of 3 slots each) + TMEM allocation
 //   warp 9          : tcgen05.mma issuer: S_w = Q_w.K_j^T, O_w += P_w.V_j, ping-ponged between the warpgroups
-// TMEM: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384).
+// TMEM: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512) (bf16 pairs).
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __restrict__ doc_start,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ lse, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = sbase + AttnFwdSmem::kQ, sK = sbase + AttnFwdSmem::kK, sV = sbase + AttnFwdSmem::kV,
-                 sP = sbase + AttnFwdSmem::kP, sBar = sbase + AttnFwdSmem::kBar;
+                 sBar = sbase + AttnFwdSmem::kBar;
   const uint32_t bQ = sBar;                                     // (tx)
   auto bKfull = [&](int s) { return sBar + 8u * (1 + s); };     // [3] (tx)
   auto bVfull = [&](int s) { return sBar + 8u * (4 + s); };     // [3] (tx)
@@ -260,7 +262,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
     __syncwarp();
   } else if (warp == 9) {
     // ============================== MMA issuer ==============================
-    if (lane == 0) {
+    {
+      const uint32_t lead = elect_one_sync();
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);
       auto issue_S = [&](int w, int slot) {
@@ -268,19 +272,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
         for (int k = 0; k < 4; ++k) {
           const uint64_t da = umma_smem_desc(sQ + w * kTileBytes + k * 32, 16, 1024);
           const uint64_t db = umma_smem_desc(sK + slot * kTileBytes + k * 32, 16, 1024);
-          umma_bf16_ss(tmem_base + w * 128, da, db, idesc_s, k > 0 ? 1u : 0u);
+          umma_bf16_ss_p(tb + w * 128, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
         }
-        tc_commit(bSfull(w));
+        tc_commit_p(bSfull(w), lead);
       };
       auto issue_PV = [&](int w, int slot, bool accumulate) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          // A = P_w (K-major, two 64-key atoms 16 KB apart); B = V (MN-major: one 128-byte row per key)
-          const uint64_t da = umma_smem_desc(sP + w * 2 * kTileBytes + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
+          // A = P_w straight from tensor memory (bf16 pairs, 8 columns per 16 keys); B = V (MN-major: one 128-byte
+          // row per key).  P never touches shared memory, whose bandwidth the S / P.V operand reads already fill.
           const uint64_t db = umma_smem_desc(sV + slot * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tmem_base + 256 + w * 64, da, db, idesc_pv, (accumulate || k > 0) ? 1u : 0u);
+          umma_bf16_ts_p(tb + 256 + w * 64, tb + 384 + w * 64 + k * 8, db, idesc_pv,
+                         (accumulate || k > 0) ? 1u : 0u, lead);
         }
-        tc_commit(bPVdone(w));
+        tc_commit_p(bPVdone(w), lead);
       };
       mbar_wait(bQ, 0);
       mbar_wait(bKfull(0), 0);
@@ -288,7 +293,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
 #pragma unroll
       for (int w = 0; w < 2; ++w)
         if (active(w, jlo)) issue_S(w, 0);
-      tc_commit(bKempty(0));
+      tc_commit_p(bKempty(0), lead);
       int idx = 0;
       for (int j = jlo; j <= jhi; ++j, ++idx) {
         const int slot = idx % 3;
@@ -315,8 +320,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
             issue_PV(w, slot, i > 0);
           }
         }
-        if (j + 1 <= jhi) tc_commit(bKempty(slot1));  // every S that reads K(j+1) has been issued
-        tc_commit(bVempty(slot));
+        if (j + 1 <= jhi) tc_commit_p(bKempty(slot1), lead);  // every S that reads K(j+1) has been issued
+        tc_commit_p(bVempty(slot), lead);
       }
     }
     __syncwarp();
@@ -331,7 +336,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       const uint32_t tS = tmem_base + lane_off + w * 128;
       const uint32_t tO = tmem_base + lane_off + 256 + w * 64;
-      const uint32_t sPw = sP + w * 2 * kTileBytes;
+      const uint32_t tP = tmem_base + lane_off + 384 + w * 64;
       constexpr float c2 = kSoftmaxScale * kLog2e;
       float ref = -INFINITY, l_run = 0.f;
       const int n_it = jmax[w] - jmin[w] + 1;
@@ -374,16 +379,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
             uint32_t pk[16];
             if (need_mask) chunk_softmax<true, true>(sr, c2, mb, lo0 - c * 32, hi0 - c * 32, pk, psum, tile_max);
             else chunk_softmax<false, true>(sr, c2, mb, 0, 0, pk, psum, tile_max);
-            if (!pv_waited) {  // P_w's shared memory is still being read by the previous tile's P.V until this fires
+            if (!pv_waited) {  // P_w in tensor memory is still being read by the previous tile's P.V until this fires
               mbar_wait(bPVdone(w), (i - 1) & 1);
+              tc_fence_after();
               pv_waited = true;
             }
-            const uint32_t prow = sPw + (c >> 1) * kTileBytes + r * 128;
-#pragma unroll
-            for (int v = 0; v < 4; ++v) {
-              const int cc = (c & 1) * 4 + v;  // 16-byte chunk index within the 128-byte half row
-              st_shared_v4(prow + ((cc ^ (r & 7)) << 4), make_uint4(pk[v * 4], pk[v * 4 + 1], pk[v * 4 + 2], pk[v * 4 + 3]));
-            }
+            tmem_st_32x32b_x16(tP + c * 16, pk);
           }
           if (!check) break;
           const bool bad = !((tile_max - ref) * c2 <= 60.f);
@@ -407,8 +408,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
           check = false;
         }
         l_run += psum.x + psum.y;
+        tmem_st_wait();
         tc_fence_before();
-        fence_proxy_async_smem();
         mbar_arrive(bPfull(w));
         TRACE(w * 2 + 0, i * 4 + 3);
       }
@@ -486,16 +487,22 @@ __global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ out, cons
 struct AttnBwdSmem {
   static constexpr int kK = 0;                      // K_j rotated
   static constexpr int kV = kK + kTileBytes;        // V_j
-  static constexpr int kQ = kV + kTileBytes;        // 2 stages, rotated Q_i
-  static constexpr int kdO = kQ + 2 * kTileBytes;   // 2 stages
-  static constexpr int kP = kdO + 2 * kTileBytes;   // 128 x 128 bf16
+  static constexpr int kStages = 3;                 // Q_i / dO_i ring
+  static constexpr int kQ = kV + kTileBytes;        // kStages x rotated Q_i
+  static constexpr int kdO = kQ + kStages * kTileBytes;
+  static constexpr int kP = kdO + kStages * kTileBytes;  // 128 x 128 bf16
   static constexpr int kdS = kP + 2 * kTileBytes;   // 128 x 128 bf16
   static constexpr int kdQ = kdS + 2 * kTileBytes;  // fp32 staging of dQ: 2 halves x (128 rows x 32 columns)
   static constexpr int kBar = kdQ + 2 * kTileBytes;
   static constexpr int kBytes = kBar + 256 + 1024;
 };
 
-__global__ void __launch_bounds__(kAttnThreads, 1)
+template <uint32_t N>
+__device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <uint32_t N>
+__device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
+__global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                 const __grid_constant__ CUtensorMap tm_dq, const float* __restrict__ cos_sin,
                 const int32_t* __restrict__ doc_start, const float* __restrict__ lse, const float* __restrict__ delta,
@@ -506,19 +513,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                  sdO = sbase + AttnBwdSmem::kdO, sP = sbase + AttnBwdSmem::kP, sdS = sbase + AttnBwdSmem::kdS,
                  sBar = sbase + AttnBwdSmem::kBar;
   const uint32_t bKVfull = sBar;                                // (tx: K and V)
-  auto bQdOfull = [&](int s) { return sBar + 8u * (2 + s); };   // [2] (tx: Q_i and dO_i)
-  auto bStageEmpty = [&](int s) { return sBar + 8u * (6 + s); };  // [2] (1, commit)
+  auto bQdOfull = [&](int s) { return sBar + 8u * (1 + s); };   // [3] (tx: Q_i and dO_i)
+  auto bStageEmpty = [&](int s) { return sBar + 8u * (4 + s); };  // [3] (1, commit)
   const uint32_t bSdPfull = sBar + 8u * 8;                      // (1, commit)
   const uint32_t bPdSfull = sBar + 8u * 9;                      // (256)
   const uint32_t bdQfull = sBar + 8u * 10;                      // (1, commit)
-  const uint32_t bdQempty = sBar + 8u * 11;                     // (256)
+  const uint32_t bdQempty = sBar + 8u * 11;                     // (128)
   const uint32_t bAccFull = sBar + 8u * 12;                     // (1, commit) dK/dV complete
   const uint32_t tmem_ptr_smem = sBar + 8u * 13;
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef PCV_TRACE
-  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 288);
+  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 416);
 #endif
   const int j = blockIdx.x;  // key tile
   const int h = blockIdx.y, b = blockIdx.z;
@@ -541,30 +548,34 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
   const int n_it = i_hi - i_lo + 1;
 
-  if (warp == 9 && lane == 0) {
+  if (warp == 13 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     tma_prefetch_desc(&tm_dq);
     mbar_init(bKVfull, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < AttnBwdSmem::kStages; ++s) {
       mbar_init(bQdOfull(s), 1);
       mbar_init(bStageEmpty(s), 1);
     }
     mbar_init(bSdPfull, 1);
     mbar_init(bPdSfull, 256);
     mbar_init(bdQfull, 1);
-    mbar_init(bdQempty, 256);
+    mbar_init(bdQempty, 128);
     mbar_init(bAccFull, 1);
     fence_mbar_init();
   }
-  if (warp == 8) tmem_alloc<512>(tmem_ptr_smem);
+  if (warp == 12) tmem_alloc<512>(tmem_ptr_smem);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
-  const uint32_t tS = tmem_base, tdP = tmem_base + 128, tdV = tmem_base + 256, tdK = tmem_base + 320, tdQ = tmem_base + 384;
+  const uint32_t tS = tmem_base, tdP = tmem_base + 128, tdV = tmem_base + 256, tdK = tmem_base + 320, tdQ = tmem_base + 384,
+                 tdS = tmem_base + 448;  // dS as bf16 pairs: the A operand of dQ = dS.K, read from tensor memory
 
-  if (warp == 8) {
+  if (warp >= 12) {
+    reg_dealloc<40>();  // warpgroup 3: producer, MMA issuer, two idle warps
+  }
+  if (warp == 12) {
     // ============================== TMA producer (q, k in qkv are already rotated) ==============================
     if (lane == 0) {
       const int row0 = static_cast<int>(seq_row0);
@@ -573,17 +584,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + h * 64, row0 + key0);
       for (int it = 0; it < n_it; ++it) {
         const int i = i_lo + it;
-        const int stage = it & 1;
-        mbar_wait(bStageEmpty(stage), ((it >> 1) & 1) ^ 1u);
+        const int stage = it % 3;
+        mbar_wait(bStageEmpty(stage), ((it / 3) & 1) ^ 1u);
         mbar_expect_tx(bQdOfull(stage), 2 * kTileBytes);
         tma_load_2d(sQ + stage * kTileBytes, &tm_qkv, bQdOfull(stage), h * 64, row0 + i * 128);
         tma_load_2d(sdO + stage * kTileBytes, &tm_do, bQdOfull(stage), h * 64, row0 + i * 128);
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
+  } else if (warp == 13) {
     // ============================== MMA issuer ==============================
-    if (lane == 0) {
+    {
+      const uint32_t lead = elect_one_sync();
+      const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t tS = tb, tdP = tb + 128, tdV = tb + 256, tdK = tb + 320, tdQ = tb + 384, tdS = tb + 448;
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);   // S, dP
       constexpr uint32_t idesc_kv = umma_idesc_bf16(128, 64, true, true);     // dV = P^T.dO, dK = dS^T.Q
       constexpr uint32_t idesc_dq = umma_idesc_bf16(128, 64, false, true);    // dQ = dS.K
@@ -594,15 +608,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         for (int k = 0; k < 4; ++k) {
           const uint64_t da = umma_smem_desc(sQ + stage * kTileBytes + k * 32, 16, 1024);
           const uint64_t db = umma_smem_desc(sK + k * 32, 16, 1024);
-          umma_bf16_ss(tS, da, db, idesc_s, k > 0 ? 1u : 0u);
+          umma_bf16_ss_p(tS, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
         }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const uint64_t da = umma_smem_desc(sdO + stage * kTileBytes + k * 32, 16, 1024);
           const uint64_t db = umma_smem_desc(sV + k * 32, 16, 1024);
-          umma_bf16_ss(tdP, da, db, idesc_s, k > 0 ? 1u : 0u);
+          umma_bf16_ss_p(tdP, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
         }
-        tc_commit(bSdPfull);
+        tc_commit_p(bSdPfull, lead);
       };
       if (n_it > 0) {
         mbar_wait(bQdOfull(0), 0);
@@ -610,7 +624,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         issue_SdP(0);
       }
       for (int it = 0; it < n_it; ++it) {
-        const int stage = it & 1;
+        const int stage = it % 3;
         const uint32_t sPb = sP, sdSb = sdS;
         TRACE(4, it * 2 + 0);
         mbar_wait(bPdSfull, it & 1);  // P/dS(it) are in shared memory; S/dP in TMEM have been consumed
@@ -618,70 +632,84 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         TRACE(4, it * 2 + 1);
         // next tile's S and dP first: they are what the compute warps wait for
         if (it + 1 < n_it) {
-          const int s1 = (it + 1) & 1;
-          mbar_wait(bQdOfull(s1), ((it + 1) >> 1) & 1);
+          const int s1 = (it + 1) % 3;
+          mbar_wait(bQdOfull(s1), ((it + 1) / 3) & 1);
           tc_fence_after();
+          TRACE(5, it * 4 + 0);
           issue_SdP(s1);
+          TRACE(5, it * 4 + 1);
         }
         mbar_wait(bdQempty, (it & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
         tc_fence_after();
+        TRACE(5, it * 4 + 2);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {  // contraction over the 128 query rows, 16 per step
           // A = P^T (MN-major view of P[q][key]: two 64-key atoms 16 KB apart); B = dO (MN-major)
           const uint64_t da = umma_smem_desc(sPb + k * 2048, kTileBytes, 1024);
           const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
+          umma_bf16_ss_p(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u, lead);
         }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const uint64_t da = umma_smem_desc(sdSb + k * 2048, kTileBytes, 1024);
           const uint64_t db = umma_smem_desc(sQ + stage * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tdK, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u);
+          umma_bf16_ss_p(tdK, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u, lead);
         }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {  // contraction over the 128 keys
-          const uint64_t da = umma_smem_desc(sdSb + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024);
           const uint64_t db = umma_smem_desc(sK + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss(tdQ, da, db, idesc_dq, k > 0 ? 1u : 0u);
+          umma_bf16_ts_p(tdQ, tdS + k * 8, db, idesc_dq, k > 0 ? 1u : 0u, lead);
         }
-        tc_commit(bdQfull);
-        tc_commit(bStageEmpty(stage));
+        tc_commit_p(bdQfull, lead);
+        tc_commit_p(bStageEmpty(stage), lead);
+        TRACE(5, it * 4 + 3);
       }
-      tc_commit(bAccFull);
+      tc_commit_p(bAccFull, lead);
     }
     __syncwarp();
-  } else {
-    // ============================== compute warps (256 threads: row r, column half `half`) ==============================
+  } else if (warp >= 8 && warp < 12) {
+    // ============================== dQ warpgroup (128 threads: one dQ row each) ==============================
+    // dQ of query tile (i_lo + it): TMEM -> fp32 staging tile in shared memory -> one TMA reduce-add per 32-column
+    // half into dq_acc (fp32, L2-side add).  Runs beside the compute warpgroups, off their critical path.
+    reg_dealloc<96>();
     const int r = tid & 127;
-    const int half = tid >> 7;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    constexpr float c2 = kSoftmaxScale * kLog2e;
-    // dQ of query tile (i_lo + itp): TMEM -> fp32 staging tile in shared memory -> one TMA reduce-add per 32-column
-    // half into dq_acc (fp32, L2-side add).
-    auto dq_readout = [&](int itp) {
-      mbar_wait(bdQfull, itp & 1);
+    const uint32_t stage_base = sbase + AttnBwdSmem::kdQ;
+    for (int it = 0; it < n_it; ++it) {
+      mbar_wait(bdQfull, it & 1);
       tc_fence_after();
-      uint32_t qr[32];
-      tmem_ld_32x32b_x32(tdQ + lane_off + half * 32, qr);
+      uint32_t q0r[32], q1r[32];
+      tmem_ld_32x32b_x32(tdQ + lane_off, q0r);
+      tmem_ld_32x32b_x32(tdQ + lane_off + 32, q1r);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bdQempty);
-      if (tid == 0) tma_store_wait_read<0>();  // earlier reduce-adds have finished reading their staging tiles
-      named_bar_sync(1, 256);
-      const uint32_t stage_base = sbase + AttnBwdSmem::kdQ;
-      const uint32_t srow = stage_base + half * kTileBytes + r * 128;
+      if (r == 0) tma_store_wait_read<0>();  // the previous reduce-add has finished reading the staging tile
+      named_bar_sync(1, 128);
+      const uint32_t srow = stage_base + r * 128;
 #pragma unroll
-      for (int v = 0; v < 8; ++v)
-        st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(qr[v * 4], qr[v * 4 + 1], qr[v * 4 + 2], qr[v * 4 + 3]));
+      for (int v = 0; v < 8; ++v) {
+        st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(q0r[v * 4], q0r[v * 4 + 1], q0r[v * 4 + 2], q0r[v * 4 + 3]));
+        st_shared_v4(srow + kTileBytes + ((v ^ (r & 7)) << 4),
+                     make_uint4(q1r[v * 4], q1r[v * 4 + 1], q1r[v * 4 + 2], q1r[v * 4 + 3]));
+      }
       fence_proxy_async_smem();
-      named_bar_sync(1, 256);
-      if (tid == 0) {
-        const int row0 = static_cast<int>(seq_row0) + (i_lo + itp) * 128;
+      named_bar_sync(1, 128);
+      if (r == 0) {
+        const int row0 = static_cast<int>(seq_row0) + (i_lo + it) * 128;
         tma_reduce_add_2d(&tm_dq, stage_base, h * 64, row0);
         tma_reduce_add_2d(&tm_dq, stage_base + kTileBytes, h * 64 + 32, row0);
         tma_store_commit();
       }
-    };
+    }
+    if (r == 0) tma_store_wait<0>();
+  } else if (warp < 8) {
+    // ============================== compute warps (256 threads: row r, column half `half`) ==============================
+    reg_alloc<168>();
+    const int r = tid & 127;
+    const int half = tid >> 7;
+    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    constexpr float c2 = kSoftmaxScale * kLog2e;
     for (int it = 0; it < n_it; ++it) {
       const int i = i_lo + it;
       const int t = i * 128 + r;
@@ -720,18 +748,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             st_shared_v4(sdS + off, make_uint4(pk_ds[c][v * 4], pk_ds[c][v * 4 + 1], pk_ds[c][v * 4 + 2], pk_ds[c][v * 4 + 3]));
           }
       }
+      // dS a second time, into tensor memory (32 columns of bf16 pairs per thread), for dQ = dS.K
+      tmem_st_32x32b_x16(tdS + lane_off + half * 32, pk_ds[0]);
+      tmem_st_32x32b_x16(tdS + lane_off + half * 32 + 16, pk_ds[1]);
+      tmem_st_wait();
       tc_fence_before();
       fence_proxy_async_smem();
       mbar_arrive(bPdSfull);
       TRACE(half, it * 4 + 2);
-      // previous tile's dQ: its MMAs were queued behind this tile's S/dP, so this runs while the tensor pipe works
-      if (it > 0) dq_readout(it - 1);
       TRACE(half, it * 4 + 3);
     }
-    // ---- tail: last dQ, then dK / dV
+    // ---- tail: dK / dV
     if (n_it > 0) {
-      dq_readout(n_it - 1);
-      if (tid == 0) tma_store_wait<0>();
       mbar_wait(bAccFull, 0);
       tc_fence_after();
       // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
@@ -770,7 +798,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == 12) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
@@ -903,7 +931,7 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
         static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, static_cast<int>(BT), T, n_heads);
   }
   dim3 grid(T / 128, n_heads, B);
-  attn_bwd_kernel<<<grid, kAttnThreads, AttnBwdSmem::kBytes, st>>>(
+  attn_bwd_kernel<<<grid, kAttnBwdThreads, AttnBwdSmem::kBytes, st>>>(
       tm_qkv, tm_do, tm_dq, cos_sin, doc_start, lse, delta, dq_acc,
       static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
   {

@@ -53,3 +53,6 @@ for hf in range(2):
 m = a[4]
 print("--- bwd MMA: (wait for PdS, then until next wait) ")
 print([(int(m[i * 2 + 1] - m[i * 2]), int(m[i * 2 + 2] - m[i * 2 + 1]) if i < 15 else -1) for i in range(16)])
+m5 = a[5]
+print("--- bwd MMA detail per tile: [PdS->QdO ready, issue SdP, wait dQempty, issue dV/dK/dQ + commits]")
+print([(int(m5[i * 4] - m[i * 2 + 1]), int(m5[i * 4 + 1] - m5[i * 4]), int(m5[i * 4 + 2] - m5[i * 4 + 1]), int(m5[i * 4 + 3] - m5[i * 4 + 2])) for i in range(15)])
