@@ -216,9 +216,9 @@ def gemm_replay_ms(model, M: int, iters: int = 3) -> float:
         for _ in range(model.cfg.n_layers):
             lin(x_d, layer.w_qkv, y_3d)
             lin(x_d, layer.w_out, o_d)
-            lin(x_d, layer.w_gu, y_2hp)
+            ops.linear_fwd_swiglu(x_d, layer.w_gu)            # gate|up GEMM, SwiGLU in its epilogue
             lin(x_hp, layer.w_down, o_d)
-            dgrad(x_d, layer.w_down, o_hp)
+            ops.linear_dgrad_dswiglu(x_d, layer.w_down, y_2hp)  # fc2 dgrad, SwiGLU backward in its epilogue
             ops.linear_wgrad(x_hp, x_d, g("layers_0.w_down"))
             dgrad(y_2hp, layer.w_gu, o_d)
             ops.linear_wgrad(x_d, y_2hp, g("layers_0.w_gu"))

@@ -70,6 +70,18 @@ int pcv_rmsnorm_residual_bwd(const void* dy, const void* dres_out, const void* r
 int pcv_swiglu_fwd(const void* gu, void* h, int M, int hid, void* stream);
 int pcv_swiglu_bwd(const void* gu, const void* dh, void* dgu, int M, int hid, void* stream);
 
+/* The GLU up-projection with its activation fused (models/LM/transformer.py:110-126): [g | u] = X[M,K] @ W_gu[K,2*hid]
+ * (fc_gate | fc_up side by side, row stride ldw) written to gu[M][ldgu] for the backward pass, and
+ * h[M][ldh] = bf16(silu(g) * u) computed from the bf16-rounded g and u in the same epilogue (each CTA pair stages
+ * 128 gate columns next to the matching 128 up columns).  Same results as pcv_gemm_bf16 + pcv_swiglu_fwd. */
+int pcv_gemm_bf16_swiglu(const void* X, const void* W_gu, void* gu, void* h, int M, int hid, int K, int ldx, int ldw,
+                         int ldgu, int ldh, void* stream);
+/* Its transpose through fc2 (transformer.py:127-134): dh = dY[M,K] @ W_down[hid,K]^T is rounded to bf16 in the
+ * epilogue and turned into [dg | du] = dgu[M][ldgu] with the saved gu; dh never reaches memory.  Same results as
+ * pcv_gemm_bf16 (dgrad) + pcv_swiglu_bwd. */
+int pcv_gemm_bf16_dswiglu(const void* dY, const void* W_down, const void* gu, void* dgu, int M, int hid, int K,
+                          int lddy, int ldw, int ldgu, void* stream);
+
 /* Y[M,N] = bf16( rope( X[M,K] @ W[K,N] ) ): the w_qkv Dense (models/LM/transformer.py:194-201) with the interleaved-pair
  * RoPE of models/LM/embedding.py:28-67 applied in the epilogue to output columns [0, rope_cols) (the q | k thirds,
  * head_dim 64) at position (row % T), in fp32 before the bf16 rounding.  cos_sin = fp32 [T][32][2] = (cos, sin) of

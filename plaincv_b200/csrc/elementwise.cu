@@ -246,7 +246,7 @@ __global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfl
     g.unpack(fg);
     u.unpack(fu);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = fg[j] / (1.f + __expf(-fg[j])) * fu[j];
+    for (int j = 0; j < 8; ++j) o[j] = swiglu_fwd_elt(fg[j], fu[j]);
     bf16x8 w;
     w.pack(o);
     *reinterpret_cast<uint4*>(h + r * hid + c) = w.raw;
@@ -270,12 +270,7 @@ __global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ gu, const __
     u.unpack(fu);
     d.unpack(fd);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float s = 1.f / (1.f + __expf(-fg[j]));
-      const float silu = fg[j] * s;
-      ou[j] = fd[j] * silu;
-      og[j] = fd[j] * fu[j] * (s + silu * (1.f - s));
-    }
+    for (int j = 0; j < 8; ++j) swiglu_bwd_elt(fg[j], fu[j], fd[j], og[j], ou[j]);
     bf16x8 wg, wu;
     wg.pack(og);
     wu.pack(ou);

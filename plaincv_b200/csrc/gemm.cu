@@ -30,6 +30,7 @@ namespace pcv {
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGemmThreads = 256;
+constexpr int kPairThreads = 384;  // CTA-pair kernel: producer, MMA, allocator, idle + 8 epilogue warps
 
 template <int BN>
 struct GemmCfg {
@@ -51,8 +52,14 @@ struct GemmParams {
   // EPI_BF16_ROPE only: interleaved-pair rotation of output columns [0, rope_cols) at position (row % T)
   const float* cos_sin;
   int T, rope_cols;
+  // EPI_SWIGLU / EPI_DSWIGLU only (CTA-pair kernel): second tensor of the fused epilogue and the column distance
+  // between the gate and the up half of a [M][2*hid] activation
+  void* aux;
+  int ld_aux, half_off;
 };
 constexpr int EPI_BF16_ROPE = 3;  // internal: PCV_EPI_BF16 + RoPE (pcv_gemm_bf16_rope)
+constexpr int EPI_SWIGLU = 4;     // internal: [g | u] = X W_gu written to C, h = silu(g) * u written to aux
+constexpr int EPI_DSWIGLU = 5;    // internal: dh = dM W_down^T kept in registers, [dg | du] written to C, gu read from aux
 
 // Work item -> (m tile, n tile, k split).  Tiles are visited in column-major order inside groups of kGroupM tile
 // rows, so the CTAs that run concurrently share a few A tiles AND a few B tiles (L2 reuse for wide outputs such as
@@ -131,6 +138,93 @@ __device__ __forceinline__ void store_row_chunk(const GemmParams& p, int row, in
           *reinterpret_cast<float4*>(crow + v * 4) = make_float4(x0, x1, x2, x3);
         }
       }
+    }
+  }
+}
+
+// ---- CTA-pair epilogue helpers: 32 accumulator columns of one row (fp32 bits in r[32]) -> 4 x 16 B of bf16.
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void pack32_bf16(const uint32_t* r, float alpha, uint4* q) {
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    q[v].x = pack_bf16x2(__uint_as_float(r[v * 8 + 0]) * alpha, __uint_as_float(r[v * 8 + 1]) * alpha);
+    q[v].y = pack_bf16x2(__uint_as_float(r[v * 8 + 2]) * alpha, __uint_as_float(r[v * 8 + 3]) * alpha);
+    q[v].z = pack_bf16x2(__uint_as_float(r[v * 8 + 4]) * alpha, __uint_as_float(r[v * 8 + 5]) * alpha);
+    q[v].w = pack_bf16x2(__uint_as_float(r[v * 8 + 6]) * alpha, __uint_as_float(r[v * 8 + 7]) * alpha);
+  }
+}
+__device__ __forceinline__ void pack32_f32(const uint32_t* r, float alpha, uint4* q) {  // 32 fp32 -> 8 x 16 B
+#pragma unroll
+  for (int v = 0; v < 8; ++v) {
+    q[v].x = __float_as_uint(__uint_as_float(r[v * 4 + 0]) * alpha);
+    q[v].y = __float_as_uint(__uint_as_float(r[v * 4 + 1]) * alpha);
+    q[v].z = __float_as_uint(__uint_as_float(r[v * 4 + 2]) * alpha);
+    q[v].w = __float_as_uint(__uint_as_float(r[v * 4 + 3]) * alpha);
+  }
+}
+// q / k columns of the fused QKV projection: rotate the 16 (even, odd) pairs of a 32-column chunk in fp32, before the
+// bf16 rounding (apply_rotary_emb_complex_like, models/LM/embedding.py:28-67); cs = 8 x (cos, sin, cos, sin).
+__device__ __forceinline__ void rope32_bf16(const uint32_t* r, const float4* cs, bool rot, float alpha, uint4* q) {
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    float x[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = __uint_as_float(r[v * 8 + k]) * alpha;
+    if (rot) {
+      const float4 c0 = cs[2 * v], c1 = cs[2 * v + 1];
+      const float a0 = x[0], b0 = x[1], a1 = x[2], b1 = x[3], a2 = x[4], b2 = x[5], a3 = x[6], b3 = x[7];
+      x[0] = a0 * c0.x - b0 * c0.y; x[1] = b0 * c0.x + a0 * c0.y;
+      x[2] = a1 * c0.z - b1 * c0.w; x[3] = b1 * c0.z + a1 * c0.w;
+      x[4] = a2 * c1.x - b2 * c1.y; x[5] = b2 * c1.x + a2 * c1.y;
+      x[6] = a3 * c1.z - b3 * c1.w; x[7] = b3 * c1.z + a3 * c1.w;
+    }
+    q[v].x = pack_bf16x2(x[0], x[1]);
+    q[v].y = pack_bf16x2(x[2], x[3]);
+    q[v].z = pack_bf16x2(x[4], x[5]);
+    q[v].w = pack_bf16x2(x[6], x[7]);
+  }
+}
+// Fused SwiGLU (GLU, models/LM/transformer.py:110-134).  Forward: g and u are rounded to bf16 first (they are Dense
+// outputs in the reference) and h = silu(g) * u is computed from the rounded values, exactly as pcv_swiglu_fwd does.
+__device__ __forceinline__ void swiglu32(const uint32_t* g, const uint32_t* u, uint4* qg, uint4* qu, uint4* qh) {
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    uint32_t* gw = reinterpret_cast<uint32_t*>(&qg[v]);
+    uint32_t* uw = reinterpret_cast<uint32_t*>(&qu[v]);
+    uint32_t* hw = reinterpret_cast<uint32_t*>(&qh[v]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      gw[k] = pack_bf16x2(__uint_as_float(g[v * 8 + 2 * k]), __uint_as_float(g[v * 8 + 2 * k + 1]));
+      uw[k] = pack_bf16x2(__uint_as_float(u[v * 8 + 2 * k]), __uint_as_float(u[v * 8 + 2 * k + 1]));
+      const float2 fg = unpack_bf16x2(gw[k]), fu = unpack_bf16x2(uw[k]);
+      hw[k] = pack_bf16x2(swiglu_fwd_elt(fg.x, fu.x), swiglu_fwd_elt(fg.y, fu.y));
+    }
+  }
+}
+// Backward: dh (32 accumulator columns, rounded to bf16 as the reference's transposed Dense output is) with the saved
+// gate / up values in qg / qu, which are overwritten by dg / du; the arithmetic is pcv_swiglu_bwd's.
+__device__ __forceinline__ void dswiglu32(const uint32_t* r, float alpha, uint4* qg, uint4* qu) {
+#pragma unroll
+  for (int v = 0; v < 4; ++v) {
+    uint32_t* gw = reinterpret_cast<uint32_t*>(&qg[v]);
+    uint32_t* uw = reinterpret_cast<uint32_t*>(&qu[v]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 fd = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[v * 8 + 2 * k]) * alpha,
+                                                  __uint_as_float(r[v * 8 + 2 * k + 1]) * alpha));
+      const float2 fg = unpack_bf16x2(gw[k]), fu = unpack_bf16x2(uw[k]);
+      float dg0, du0, dg1, du1;
+      swiglu_bwd_elt(fg.x, fu.x, fd.x, dg0, du0);
+      swiglu_bwd_elt(fg.y, fu.y, fd.y, dg1, du1);
+      gw[k] = pack_bf16x2(dg0, dg1);
+      uw[k] = pack_bf16x2(du0, du1);
     }
   }
 }
@@ -305,21 +399,26 @@ struct PairCfg {
   static constexpr int kBBytes = 128 * kBK * 2;  // this CTA's 128 of the 256 B rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarBytes = 256;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;
+  static constexpr int kEpiWarps = 8;
+  static constexpr int kEpiBufBytes = 32 * 128;  // per epilogue warp: 32 rows x 128 B (one 128B-swizzled TMA box)
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + kBarBytes + 1024;
   static constexpr uint32_t kTmemCols = 512;  // two 256-column accumulators
 };
+static_assert(PairCfg::kSmemBytes <= 232448, "CTA-pair GEMM shared memory exceeds 227 KB");
 
 template <bool A_MN, bool B_MN, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                      const GemmParams p) {
+                      const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
+                      const __grid_constant__ CUtensorMap tma_x, const GemmParams p) {
   using Cfg = PairCfg;
   constexpr int BN = Cfg::kBN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_a = smem_base;
   const uint32_t smem_b = smem_base + Cfg::kStages * Cfg::kABytes;
-  const uint32_t bar_base = smem_base + Cfg::kStages * Cfg::kStageBytes;
+  const uint32_t smem_epi = smem_base + Cfg::kStages * Cfg::kStageBytes;  // 1024-aligned: stages are 32 KB
+  const uint32_t bar_base = smem_epi + Cfg::kEpiWarps * Cfg::kEpiBufBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (Cfg::kStages + s); };
   auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * Cfg::kStages + s); };
@@ -337,6 +436,9 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    tma_prefetch_desc(&tma_c);
+    tma_prefetch_desc(&tma_c2);
+    tma_prefetch_desc(&tma_x);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < Cfg::kStages; ++s) {
@@ -345,7 +447,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);   // multicast tcgen05.commit
-      mbar_init(tmem_empty_bar(s), 8);  // leader: 4 epilogue warps of each CTA
+      mbar_init(tmem_empty_bar(s), 16);  // leader: 8 epilogue warps of each CTA
     }
     fence_mbar_init();
   }
@@ -370,7 +472,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         const int m0 = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128;
-        const int n0 = n_blk * BN + static_cast<int>(rank) * 128;
+        // fused SwiGLU forward: the tile is 128 gate columns (staged by CTA 0) next to the matching 128 up columns
+        // (staged by CTA 1), so every epilogue thread holds g and u of the same hidden unit
+        const int n0 = (EPI == EPI_SWIGLU) ? n_blk * 128 + static_cast<int>(rank) * p.half_off
+                                           : n_blk * BN + static_cast<int>(rank) * 128;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * Cfg::kStageBytes);
@@ -434,30 +539,163 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     __syncwarp();
   } else if (warp >= 4) {
     // ===================== epilogue (each CTA drains its own 128 accumulator rows) =====================
+    // 8 warps: warp (ew, hh) owns TMEM lanes [32 ew, 32 ew + 32) (its row quarter) and column half hh of the tile.
+    // Results leave through a per-warp 32 x 128 B staging box in shared memory and one TMA store (fp32 reduce-add for
+    // the wgrad epilogue) per box: whole 128-byte lines reach L2 instead of one 16-byte piece per row per instruction.
     const int ew = warp & 3;
+    const int hh = (warp - 4) >> 2;
+    const uint32_t buf = smem_epi + static_cast<uint32_t>(warp - 4) * Cfg::kEpiBufBytes;
+    const uint32_t my_row = buf + lane * 128;
+    const uint32_t sw = lane & 7;
+    auto put = [&](const CUtensorMap* m, const uint4* q, int c0, int r0) {
+      if (lane == 0) tma_store_wait_read<0>();  // the previous box has been read out of the buffer
+      __syncwarp();
+#pragma unroll
+      for (int v = 0; v < 8; ++v) st_shared_v4(my_row + ((v ^ sw) << 4), q[v]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (EPI == PCV_EPI_F32_ATOMIC) tma_reduce_add_2d(m, buf, c0, r0);
+        else tma_store_2d(m, buf, c0, r0);
+        tma_store_commit();
+      }
+    };
     int it = 0;
     for (int w = pair; w < total_work; w += npairs, ++it) {
       int m_blk, n_blk, split_unused;
       decode_work(p, w, m_blk, n_blk, split_unused);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
-      mbar_wait(tmem_full_bar(acc), acc_phase);
-      tc_fence_after();
-      const int row = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128 + ew * 32 + lane;
-      const int n0 = n_blk * BN;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN;
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (row < p.M && col0 < p.N) store_row_chunk<EPI>(p, row, col0, r);
+      const int row0 = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128 + ew * 32;  // first row of this warp's boxes
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + hh * 128;
+      auto release = [&]() {  // this warp has read its part of the accumulator: hand it back to the MMA issuer
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa_shared(tmem_empty_bar(acc), 0));
+      };
+      if constexpr (EPI == EPI_SWIGLU) {
+        // accumulator columns [0,128) = gate, [128,256) = up of hidden units [n_blk*128, +128); this warp: 64 of them
+        const int n0 = n_blk * 128 + hh * 64;
+        const uint32_t tg = taddr - hh * 128 + hh * 64;
+        mbar_wait(tmem_full_bar(acc), acc_phase);
+        tc_fence_after();
+        uint4 qg[8], qu[8], qh[8];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t g[32], u[32];
+          tmem_ld_32x32b_x32(tg + c * 32, g);
+          tmem_ld_32x32b_x32(tg + 128 + c * 32, u);
+          tmem_ld_wait();
+          if (c == 1) release();
+          swiglu32(g, u, qg + 4 * c, qu + 4 * c, qh + 4 * c);
+        }
+        if (n0 < p.N) {
+          put(&tma_c, qg, n0, row0);
+          put(&tma_c2, qu, n0, row0);
+          put(&tma_x, qh, n0, row0);
+        }
+      } else if constexpr (EPI == EPI_DSWIGLU) {
+        const int n0 = n_blk * BN + hh * 128;
+        const __nv_bfloat16* gu = reinterpret_cast<const __nv_bfloat16*>(p.aux);
+        uint4 pg[8], pu[8];
+        // coalesced fetch of a 32-row x 64-column slab of g and of u: lane -> (row 4i + lane/8, 16-byte piece lane%8)
+        auto fetch = [&](int c0) {
+          const int c = c0 + (lane & 7) * 8;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = row0 + 4 * i + (lane >> 3);
+            const bool ok = r < p.M && c + 8 <= p.N;
+            const __nv_bfloat16* src = gu + static_cast<size_t>(r) * p.ld_aux + c;
+            pg[i] = ok ? __ldg(reinterpret_cast<const uint4*>(src)) : make_uint4(0, 0, 0, 0);
+            pu[i] = ok ? __ldg(reinterpret_cast<const uint4*>(src + p.half_off)) : make_uint4(0, 0, 0, 0);
+          }
+        };
+        // pieces -> through the staging box -> this lane's own row (8 pieces = 64 columns)
+        auto transpose = [&](uint4* pcs) {
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t rr = 4 * i + (lane >> 3);
+            st_shared_v4(buf + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4), pcs[i]);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int v = 0; v < 8; ++v) pcs[v] = ld_shared_v4(my_row + ((v ^ sw) << 4));
+          __syncwarp();
+        };
+        fetch(n0);  // gu is an input of the launch: fetched while the MMAs of this tile still run
+        mbar_wait(tmem_full_bar(acc), acc_phase);
+        tc_fence_after();
+#pragma unroll
+        for (int sl = 0; sl < 2; ++sl) {
+          transpose(pg);
+          transpose(pu);
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + sl * 64 + half * 32, r);
+            tmem_ld_wait();
+            if (sl == 1 && half == 1) release();
+            dswiglu32(r, p.alpha, pg + 4 * half, pu + 4 * half);
+          }
+          if (n0 + sl * 64 < p.N) {
+            put(&tma_c, pg, n0 + sl * 64, row0);
+            put(&tma_c2, pu, n0 + sl * 64, row0);
+          }
+          if (sl == 0) fetch(n0 + 64);
+        }
+      } else if constexpr (EPI == EPI_BF16_ROPE || EPI == PCV_EPI_BF16) {
+        const int n0 = n_blk * BN + hh * 128;
+        // (cos, sin) of this row's position for the 32 pairs of a head: the same for every head of the tile, so they
+        // are fetched once per tile, before the accumulator is waited for
+        const bool rot = (EPI == EPI_BF16_ROPE) && n0 < p.rope_cols;
+        float4 cs[16];
+        if constexpr (EPI == EPI_BF16_ROPE) {
+          if (rot) {
+            const int row = min(row0 + lane, p.M - 1);
+            const float4* src = reinterpret_cast<const float4*>(p.cos_sin + static_cast<size_t>(row % p.T) * 64);
+#pragma unroll
+            for (int v = 0; v < 16; ++v) cs[v] = __ldg(src + v);
+          }
+        }
+        mbar_wait(tmem_full_bar(acc), acc_phase);
+        tc_fence_after();
+#pragma unroll
+        for (int sl = 0; sl < 2; ++sl) {
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32b_x32(taddr + sl * 64, r0);
+          tmem_ld_32x32b_x32(taddr + sl * 64 + 32, r1);
+          tmem_ld_wait();
+          if (sl == 1) release();
+          uint4 q[8];
+          if constexpr (EPI == EPI_BF16_ROPE) {
+            rope32_bf16(r0, cs, rot, p.alpha, q);
+            rope32_bf16(r1, cs + 8, rot, p.alpha, q + 4);
+          } else {
+            pack32_bf16(r0, p.alpha, q);
+            pack32_bf16(r1, p.alpha, q + 4);
+          }
+          if (n0 + sl * 64 < p.N) put(&tma_c, q, n0 + sl * 64, row0);
+        }
+      } else {  // fp32 store / fp32 reduce-add: boxes of 32 columns
+        const int n0 = n_blk * BN + hh * 128;
+        mbar_wait(tmem_full_bar(acc), acc_phase);
+        tc_fence_after();
+#pragma unroll
+        for (int sl = 0; sl < 4; ++sl) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + sl * 32, r);
+          tmem_ld_wait();
+          if (sl == 3) release();
+          uint4 q[8];
+          pack32_f32(r, p.alpha, q);
+          if (n0 + sl * 32 < p.N) put(&tma_c, q, n0 + sl * 32, row0);
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(mapa_shared(tmem_empty_bar(acc), 0));
     }
+    if (lane == 0) tma_store_wait<0>();  // every box has left shared memory and reached global memory
+    __syncwarp();
   }
 
   tc_fence_before();
@@ -606,9 +844,15 @@ static int dispatch_major(int a_mn, int b_mn, int epi, const CUtensorMap& ta, co
 }
 
 
+// Output tensor maps of the CTA-pair kernel (boxes of 32 rows x 128 bytes): c = C (or the gate / dg half), c2 = the up /
+// du half, x = h of the fused SwiGLU forward.  Unused ones repeat c.
+struct PairOut {
+  CUtensorMap c, c2, x;
+};
+
 template <bool A_MN, bool B_MN, int EPI>
-static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
-                            cudaStream_t st) {
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const PairOut& o, const GemmParams& p,
+                            int grid, cudaStream_t st) {
   auto kern = gemm_bf16_pair_kernel<A_MN, B_MN, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -616,31 +860,37 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_set = true;
   }
-  kern<<<grid, kGemmThreads, PairCfg::kSmemBytes, st>>>(ta, tb, p);  // __cluster_dims__(2,1,1): grid is even
+  kern<<<grid, kPairThreads, PairCfg::kSmemBytes, st>>>(ta, tb, o.c, o.c2, o.x, p);  // __cluster_dims__(2,1,1): grid is even
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
 }
 
 template <bool A_MN, bool B_MN>
-static int dispatch_epi_pair(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
-                             cudaStream_t st) {
+static int dispatch_epi_pair(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const PairOut& o,
+                             const GemmParams& p, int grid, cudaStream_t st) {
   switch (epi) {
-    case PCV_EPI_BF16: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_BF16>(ta, tb, p, grid, st);
-    case PCV_EPI_F32_ATOMIC: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32_ATOMIC>(ta, tb, p, grid, st);
-    case PCV_EPI_F32: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32>(ta, tb, p, grid, st);
+    case PCV_EPI_BF16: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_BF16>(ta, tb, o, p, grid, st);
+    case PCV_EPI_F32_ATOMIC: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32_ATOMIC>(ta, tb, o, p, grid, st);
+    case PCV_EPI_F32: return launch_gemm_pair<A_MN, B_MN, PCV_EPI_F32>(ta, tb, o, p, grid, st);
     case EPI_BF16_ROPE:
-      if constexpr (!A_MN && B_MN) return launch_gemm_pair<A_MN, B_MN, EPI_BF16_ROPE>(ta, tb, p, grid, st);
+      if constexpr (!A_MN && B_MN) return launch_gemm_pair<A_MN, B_MN, EPI_BF16_ROPE>(ta, tb, o, p, grid, st);
+      else return PCV_ERR_ARG;
+    case EPI_SWIGLU:
+      if constexpr (!A_MN && B_MN) return launch_gemm_pair<A_MN, B_MN, EPI_SWIGLU>(ta, tb, o, p, grid, st);
+      else return PCV_ERR_ARG;
+    case EPI_DSWIGLU:
+      if constexpr (!A_MN && !B_MN) return launch_gemm_pair<A_MN, B_MN, EPI_DSWIGLU>(ta, tb, o, p, grid, st);
       else return PCV_ERR_ARG;
   }
   return PCV_ERR_ARG;
 }
 
 static int dispatch_major_pair(int a_mn, int b_mn, int epi, const CUtensorMap& ta, const CUtensorMap& tb,
-                               const GemmParams& p, int grid, cudaStream_t st) {
-  if (!a_mn && !b_mn) return dispatch_epi_pair<false, false>(epi, ta, tb, p, grid, st);
-  if (!a_mn && b_mn) return dispatch_epi_pair<false, true>(epi, ta, tb, p, grid, st);
-  if (a_mn && !b_mn) return dispatch_epi_pair<true, false>(epi, ta, tb, p, grid, st);
-  return dispatch_epi_pair<true, true>(epi, ta, tb, p, grid, st);
+                               const PairOut& o, const GemmParams& p, int grid, cudaStream_t st) {
+  if (!a_mn && !b_mn) return dispatch_epi_pair<false, false>(epi, ta, tb, o, p, grid, st);
+  if (!a_mn && b_mn) return dispatch_epi_pair<false, true>(epi, ta, tb, o, p, grid, st);
+  if (a_mn && !b_mn) return dispatch_epi_pair<true, false>(epi, ta, tb, o, p, grid, st);
+  return dispatch_epi_pair<true, true>(epi, ta, tb, o, p, grid, st);
 }
 
 
@@ -708,9 +958,16 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       p.kb_total = kb_total; p.kb_per_split = kps; p.splits = sp;
       p.alpha = alpha;
       p.cos_sin = cos_sin; p.T = T; p.rope_cols = rope_cols;
+      p.aux = nullptr; p.ld_aux = 0; p.half_off = 0;
+      PairOut o;
+      if (epilogue == PCV_EPI_BF16 || epilogue == EPI_BF16_ROPE) rc = get_tmap_2d_bf16(&o.c, C, M, N, ldc, 32);
+      else rc = get_tmap_2d_f32(&o.c, C, M, N, ldc, 32);
+      if (rc) return rc;
+      o.c2 = o.c;
+      o.x = o.c;
       const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
       count_launch();
-      return dispatch_major_pair(a_mn_major, b_mn_major, epilogue, ta, tb, p, static_cast<int>(2 * pairs), st);
+      return dispatch_major_pair(a_mn_major, b_mn_major, epilogue, ta, tb, o, p, static_cast<int>(2 * pairs), st);
     }
   }
 
@@ -740,6 +997,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   p.splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.alpha = alpha;
   p.cos_sin = cos_sin; p.T = T; p.rope_cols = rope_cols;
+  p.aux = nullptr; p.ld_aux = 0; p.half_off = 0;
   const long total = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
   count_launch();
@@ -757,4 +1015,56 @@ extern "C" int pcv_gemm_bf16_rope(const void* X, const void* W, void* Y, int M, 
                                   const float* cos_sin, int T, int rope_cols, void* stream) {
   if (!cos_sin || T <= 0 || rope_cols < 0 || rope_cols > N || rope_cols % 64 || M % T) return PCV_ERR_ARG;
   return gemm_impl(X, W, Y, M, N, K, ldx, ldw, ldy, 0, 1, pcv::EPI_BF16_ROPE, 1, 1.0f, cos_sin, T, rope_cols, stream);
+}
+
+// Fused SwiGLU GEMMs: always CTA-pair tiles (the gate | up pairing of the forward needs the two B halves of a pair).
+static int gemm_swiglu_impl(bool bwd, const void* A, const void* W, void* C, void* aux, int M, int hid, int K, int lda,
+                            int ldw, int ldc, int ld_aux, float alpha, void* stream) {
+  using namespace pcv;
+  if (M <= 0 || hid <= 0 || K <= 0 || !A || !W || !C || !aux) return PCV_ERR_ARG;
+  if (hid % 8 || ldc % 8 || ld_aux % 8 || (reinterpret_cast<uintptr_t>(C) & 15) || (reinterpret_cast<uintptr_t>(aux) & 15))
+    return PCV_ERR_ALIGN;
+  CUtensorMap ta, tb;
+  int rc = get_tmap_2d_bf16(&ta, A, M, K, lda, 128);
+  if (rc) return rc;
+  // forward: W_gu stored [K][2*hid] (MN-major B, boxes of 64 columns); backward: W_down stored [hid][K] (K-major B)
+  if (!bwd) rc = get_tmap_2d_bf16(&tb, W, K, 2 * static_cast<uint64_t>(hid), ldw, 64);
+  else rc = get_tmap_2d_bf16(&tb, W, hid, K, ldw, 128);
+  if (rc) return rc;
+  GemmParams p;
+  p.C = C;
+  p.M = M; p.N = hid; p.K = K; p.ldc = ldc;
+  p.m_tiles = (M + 255) / 256;
+  p.n_tiles = bwd ? (hid + 255) / 256 : (hid + 127) / 128;
+  p.kb_total = (K + kBK - 1) / kBK; p.kb_per_split = p.kb_total; p.splits = 1;
+  p.alpha = alpha;
+  p.cos_sin = nullptr; p.T = 1; p.rope_cols = 0;
+  p.aux = aux; p.ld_aux = ld_aux; p.half_off = hid;
+  // outputs: the gate (dg) and the up (du) half of C = [M][2*hid] as two maps clipped at hid columns, and h
+  PairOut o;
+  __nv_bfloat16* cb = static_cast<__nv_bfloat16*>(C);
+  rc = get_tmap_2d_bf16(&o.c, cb, M, hid, ldc, 32);
+  if (rc) return rc;
+  rc = get_tmap_2d_bf16(&o.c2, cb + hid, M, hid, ldc, 32);
+  if (rc) return rc;
+  if (!bwd) rc = get_tmap_2d_bf16(&o.x, aux, M, hid, ld_aux, 32);
+  else o.x = o.c;
+  if (rc) return rc;
+  const long t2 = static_cast<long>(p.m_tiles) * p.n_tiles;
+  const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
+  count_launch();
+  return dispatch_major_pair(0, bwd ? 0 : 1, bwd ? EPI_DSWIGLU : EPI_SWIGLU, ta, tb, o, p, static_cast<int>(2 * pairs),
+                             static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int pcv_gemm_bf16_swiglu(const void* X, const void* W_gu, void* gu, void* h, int M, int hid, int K, int ldx,
+                                    int ldw, int ldgu, int ldh, void* stream) {
+  if (ldgu < 2 * hid || ldh < hid || ldw < 2 * hid) return PCV_ERR_ARG;
+  return gemm_swiglu_impl(false, X, W_gu, gu, h, M, hid, K, ldx, ldw, ldgu, ldh, 1.0f, stream);
+}
+
+extern "C" int pcv_gemm_bf16_dswiglu(const void* dY, const void* W_down, const void* gu, void* dgu, int M, int hid,
+                                     int K, int lddy, int ldw, int ldgu, void* stream) {
+  if (ldgu < 2 * hid || ldw < K) return PCV_ERR_ARG;
+  return gemm_swiglu_impl(true, dY, W_down, dgu, const_cast<void*>(gu), M, hid, K, lddy, ldw, ldgu, ldgu, 1.0f, stream);
 }

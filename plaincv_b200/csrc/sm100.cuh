@@ -310,4 +310,21 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
   return __bfloat1622float2(b);
 }
 
+
+// silu(g) = g * sigmoid(g) and its pieces, shared by the stand-alone SwiGLU kernels and the fused GEMM epilogues so
+// that both produce the same bits: sigmoid = rcp.approx(1 + ex2.approx(-g * log2 e)) (2 MUFU ops, no IEEE division).
+__device__ __forceinline__ float sigmoid_fast(float g) {
+  float e, s;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(g * -1.4426950408889634f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(1.f + e));
+  return s;
+}
+__device__ __forceinline__ float swiglu_fwd_elt(float g, float u) { return g * sigmoid_fast(g) * u; }
+__device__ __forceinline__ void swiglu_bwd_elt(float g, float u, float dh, float& dg, float& du) {
+  const float s = sigmoid_fast(g);
+  const float silu = g * s;
+  du = dh * silu;
+  dg = dh * u * (s + silu * (1.f - s));
+}
+
 }  // namespace pcv

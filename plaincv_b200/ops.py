@@ -62,6 +62,28 @@ def linear_fwd_rope(x: torch.Tensor, w: torch.Tensor, cos_sin: torch.Tensor, T: 
     return y
 
 
+def linear_fwd_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(gu, h): gu[M,2*hid] = x @ [fc_gate | fc_up] and h = silu(g) * u from one GEMM launch (fused epilogue)."""
+    M, K = x.shape
+    two_h = w_gu.shape[1]
+    hid = two_h // 2
+    gu = torch.empty((M, two_h), dtype=torch.bfloat16, device=x.device)
+    h = torch.empty((M, hid), dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().pcv_gemm_bf16_swiglu(x.data_ptr(), w_gu.data_ptr(), gu.data_ptr(), h.data_ptr(), M, hid, K, K,
+                                           two_h, two_h, hid, _stream()), "pcv_gemm_bf16_swiglu")
+    return gu, h
+
+
+def linear_dgrad_dswiglu(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    """dgu[M,2*hid] = swiglu'(gu) applied to dh = dy[M,d] @ w_down[hid,d]^T, dh never materialised."""
+    M, K = dy.shape
+    hid = w_down.shape[0]
+    dgu = torch.empty_like(gu)
+    check(_lib.load().pcv_gemm_bf16_dswiglu(dy.data_ptr(), w_down.data_ptr(), gu.data_ptr(), dgu.data_ptr(), M, hid, K,
+                                            K, w_down.shape[1], gu.shape[1], _stream()), "pcv_gemm_bf16_dswiglu")
+    return dgu
+
+
 def rope_qk_(qkv: torch.Tensor, cos_sin: torch.Tensor, B: int, T: int, n_heads: int) -> torch.Tensor:
     """In-place RoPE of the q | k columns of qkv (stand-alone form of the fused epilogue above)."""
     check(_lib.load().pcv_rope_qk(qkv.data_ptr(), cos_sin.data_ptr(), B, T, n_heads, _stream()), "pcv_rope_qk")
@@ -309,8 +331,7 @@ class BlockFn(torch.autograd.Function):
         a = linear_fwd(o, layer.w_out)
         res2, h2, rstd2 = rmsnorm_residual_fwd(res1, a, layer.mlp_norm, eps)
         del a
-        gu = linear_fwd(h2, layer.w_gu)
-        hh = swiglu_fwd(gu)
+        gu, hh = linear_fwd_swiglu(h2, layer.w_gu)
         m = linear_fwd(hh, layer.w_down)
         ctx.save_for_backward(res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh)
         ctx.layer, ctx.rt, ctx.has_delta = layer, rt, delta is not None
@@ -322,10 +343,8 @@ class BlockFn(torch.autograd.Function):
         layer, rt = ctx.layer, ctx.rt
         d_m = d_m.contiguous()
         # MLP branch
-        d_hh = linear_dgrad(d_m, layer.w_down)
+        d_gu = linear_dgrad_dswiglu(d_m, layer.w_down, gu)
         linear_wgrad(hh, d_m, layer.g_down)
-        d_gu = swiglu_bwd(gu, d_hh)
-        del d_hh
         d_h2 = linear_dgrad(d_gu, layer.w_gu)
         linear_wgrad(h2, d_gu, layer.g_gu)
         del d_gu

