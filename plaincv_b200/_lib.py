@@ -78,6 +78,12 @@ def load() -> ctypes.CDLL:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
         fn.restype = restype
         fn.argtypes = argtypes
+    # measurement switches (A/B runs only): PCV_GEMM_MODE = 0 auto | 1 single-CTA tiles | 2 CTA-pair tiles,
+    # PCV_GEMM_TAIL = 0 keeps the last partial wave of a CTA-pair GEMM as full 256x256 tiles
+    if "PCV_GEMM_MODE" in os.environ:
+        lib.pcv_gemm_set_mode(int(os.environ["PCV_GEMM_MODE"]))
+    if "PCV_GEMM_TAIL" in os.environ:
+        lib.pcv_gemm_set_mode(4 if os.environ["PCV_GEMM_TAIL"] != "0" else 3)
     _lib = lib
     return lib
 

@@ -56,6 +56,9 @@ struct GemmParams {
   // between the gate and the up half of a [M][2*hid] activation
   void* aux;
   int ld_aux, half_off;
+  // CTA-pair kernel, tail of the persistent schedule: the tiles of the last, partial wave (index >= full_tiles) are cut
+  // into two 256 x 128 halves when that lets every pair work on it (narrow = 1), instead of leaving pairs idle
+  int full_tiles, narrow;
 };
 constexpr int EPI_BF16_ROPE = 3;  // internal: PCV_EPI_BF16 + RoPE (pcv_gemm_bf16_rope)
 constexpr int EPI_SWIGLU = 4;     // internal: [g | u] = X W_gu written to C, h = silu(g) * u written to aux
@@ -78,6 +81,28 @@ __device__ __forceinline__ void decode_work(const GemmParams& p, int w, int& m_b
   n_blk = r / gm;
 }
 
+
+// CTA-pair schedule: work index -> tile, k split and (for the halved tail tiles) which 128-column half.
+struct PairWork {
+  int m_blk, n_blk, split, ncol0, narrow;
+};
+__device__ __forceinline__ PairWork decode_pair_work(const GemmParams& p, int w) {
+  PairWork r;
+  r.ncol0 = 0;
+  r.narrow = 0;
+  if (p.narrow && w >= p.full_tiles) {
+    const int u = w - p.full_tiles;
+    r.narrow = 1;
+    r.ncol0 = (u & 1) * 128;
+    w = p.full_tiles + (u >> 1);
+  }
+  decode_work(p, w, r.m_blk, r.n_blk, r.split);
+  return r;
+}
+__device__ __forceinline__ int pair_total_work(const GemmParams& p) {
+  const int tiles = p.m_tiles * p.n_tiles * p.splits;
+  return p.narrow ? p.full_tiles + 2 * (tiles - p.full_tiles) : tiles;
+}
 
 // One thread's 32 consecutive accumulator columns of one output row -> global memory.
 template <int EPI>
@@ -409,8 +434,9 @@ static_assert(PairCfg::kSmemBytes <= 232448, "CTA-pair GEMM shared memory exceed
 template <bool A_MN, bool B_MN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                      const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_c2,
-                      const __grid_constant__ CUtensorMap tma_x, const GemmParams p) {
+                      const __grid_constant__ CUtensorMap tma_bn, const __grid_constant__ CUtensorMap tma_c,
+                      const __grid_constant__ CUtensorMap tma_c2, const __grid_constant__ CUtensorMap tma_x,
+                      const GemmParams p) {
   using Cfg = PairCfg;
   constexpr int BN = Cfg::kBN;
   extern __shared__ uint8_t smem_raw[];
@@ -436,6 +462,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
+    tma_prefetch_desc(&tma_bn);
     tma_prefetch_desc(&tma_c);
     tma_prefetch_desc(&tma_c2);
     tma_prefetch_desc(&tma_x);
@@ -459,7 +486,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
 
-  const int total_work = p.m_tiles * p.n_tiles * p.splits;
+  const int total_work = pair_total_work(p);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -467,18 +494,20 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       int stage = 0;
       uint32_t phase = 0;
       for (int w = pair; w < total_work; w += npairs) {
-        int m_blk, n_blk, split;
-        decode_work(p, w, m_blk, n_blk, split);
-        const int kb0 = split * p.kb_per_split;
+        const PairWork wk = decode_pair_work(p, w);
+        const int kb0 = wk.split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
-        const int m0 = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128;
-        // fused SwiGLU forward: the tile is 128 gate columns (staged by CTA 0) next to the matching 128 up columns
-        // (staged by CTA 1), so every epilogue thread holds g and u of the same hidden unit
-        const int n0 = (EPI == EPI_SWIGLU) ? n_blk * 128 + static_cast<int>(rank) * p.half_off
-                                           : n_blk * BN + static_cast<int>(rank) * 128;
+        const int m0 = wk.m_blk * Cfg::kTileM + static_cast<int>(rank) * 128;
+        // this CTA's share of the B tile: 128 of 256 rows, or 64 of 128 for a halved tail tile.  Fused SwiGLU forward:
+        // the tile is 128 gate columns (staged by CTA 0) next to the matching 128 up columns (staged by CTA 1), so
+        // every epilogue thread holds g and u of the same hidden unit
+        const int n0 = (EPI == EPI_SWIGLU) ? wk.n_blk * 128 + static_cast<int>(rank) * p.half_off
+                       : wk.narrow         ? wk.n_blk * BN + wk.ncol0 + static_cast<int>(rank) * 64
+                                           : wk.n_blk * BN + static_cast<int>(rank) * 128;
+        const uint32_t tx = wk.narrow ? 2 * (Cfg::kABytes + Cfg::kBBytes / 2) : 2 * Cfg::kStageBytes;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * Cfg::kStageBytes);
+          if (rank == 0) mbar_expect_tx(full_bar(stage), tx);
           const uint32_t bar = mapa_shared(full_bar(stage), 0);
           const uint32_t sa = smem_a + stage * Cfg::kABytes;
           const uint32_t sb = smem_b + stage * Cfg::kBBytes;
@@ -490,10 +519,11 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             for (int i = 0; i < 2; ++i) tma_load_2d_pair(sa + i * (64 * kBK * 2), &tma_a, bar, m0 + 64 * i, k0);
           }
           if constexpr (!B_MN) {
-            tma_load_2d_pair(sb, &tma_b, bar, k0, n0);
+            if (wk.narrow) tma_load_2d_pair(sb, &tma_bn, bar, k0, n0);
+            else tma_load_2d_pair(sb, &tma_b, bar, k0, n0);
           } else {
-#pragma unroll
-            for (int i = 0; i < 2; ++i) tma_load_2d_pair(sb + i * (64 * kBK * 2), &tma_b, bar, n0 + 64 * i, k0);
+            tma_load_2d_pair(sb, &tma_b, bar, n0, k0);
+            if (!wk.narrow) tma_load_2d_pair(sb + 64 * kBK * 2, &tma_b, bar, n0 + 64, k0);
           }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
         }
@@ -503,7 +533,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   } else if (warp == 1) {
     if (lane == 0 && rank == 0) {
       // ===================== MMA issuer (leader CTA only) =====================
-      constexpr uint32_t idesc = umma_idesc_bf16(256, BN, A_MN, B_MN);
+      constexpr uint32_t idesc_full = umma_idesc_bf16(256, BN, A_MN, B_MN);
+      constexpr uint32_t idesc_half = umma_idesc_bf16(256, BN / 2, A_MN, B_MN);
       constexpr uint32_t a_kstep = A_MN ? 16 * 128 : 32;
       constexpr uint32_t b_kstep = B_MN ? 16 * 128 : 32;
       constexpr uint32_t a_lbo = A_MN ? 64 * kBK * 2 : 16, b_lbo = B_MN ? 64 * kBK * 2 : 16;
@@ -511,9 +542,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       uint32_t phase = 0;
       int it = 0;
       for (int w = pair; w < total_work; w += npairs, ++it) {
-        const int split = w / (p.n_tiles * p.m_tiles);
-        const int kb0 = split * p.kb_per_split;
+        const PairWork wk = decode_pair_work(p, w);
+        const int kb0 = wk.split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const uint32_t idesc = wk.narrow ? idesc_half : idesc_full;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         mbar_wait(tmem_empty_bar(acc), acc_phase ^ 1u);
@@ -562,12 +594,15 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     };
     int it = 0;
     for (int w = pair; w < total_work; w += npairs, ++it) {
-      int m_blk, n_blk, split_unused;
-      decode_work(p, w, m_blk, n_blk, split_unused);
+      const PairWork wk = decode_pair_work(p, w);
+      const int m_blk = wk.m_blk, n_blk = wk.n_blk;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       const int row0 = m_blk * Cfg::kTileM + static_cast<int>(rank) * 128 + ew * 32;  // first row of this warp's boxes
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + hh * 128;
+      // this warp's columns: half of a full tile (two 64-column slabs), a quarter of a halved tail tile (one slab)
+      const int nslab = wk.narrow ? 1 : 2;
+      const int tcol = wk.narrow ? hh * 64 : hh * 128;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + tcol;
       auto release = [&]() {  // this warp has read its part of the accumulator: hand it back to the MMA issuer
         tc_fence_before();
         __syncwarp();
@@ -576,7 +611,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       if constexpr (EPI == EPI_SWIGLU) {
         // accumulator columns [0,128) = gate, [128,256) = up of hidden units [n_blk*128, +128); this warp: 64 of them
         const int n0 = n_blk * 128 + hh * 64;
-        const uint32_t tg = taddr - hh * 128 + hh * 64;
+        const uint32_t tg = taddr - tcol + hh * 64;
         mbar_wait(tmem_full_bar(acc), acc_phase);
         tc_fence_after();
         uint4 qg[8], qu[8], qh[8];
@@ -646,7 +681,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           if (sl == 0) fetch(n0 + 64);
         }
       } else if constexpr (EPI == EPI_BF16_ROPE || EPI == PCV_EPI_BF16) {
-        const int n0 = n_blk * BN + hh * 128;
+        const int n0 = n_blk * BN + wk.ncol0 + tcol;
         // (cos, sin) of this row's position for the 32 pairs of a head: the same for every head of the tile, so they
         // are fetched once per tile, before the accumulator is waited for
         const bool rot = (EPI == EPI_BF16_ROPE) && n0 < p.rope_cols;
@@ -663,34 +698,38 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         tc_fence_after();
 #pragma unroll
         for (int sl = 0; sl < 2; ++sl) {
-          uint32_t r0[32], r1[32];
-          tmem_ld_32x32b_x32(taddr + sl * 64, r0);
-          tmem_ld_32x32b_x32(taddr + sl * 64 + 32, r1);
-          tmem_ld_wait();
-          if (sl == 1) release();
-          uint4 q[8];
-          if constexpr (EPI == EPI_BF16_ROPE) {
-            rope32_bf16(r0, cs, rot, p.alpha, q);
-            rope32_bf16(r1, cs + 8, rot, p.alpha, q + 4);
-          } else {
-            pack32_bf16(r0, p.alpha, q);
-            pack32_bf16(r1, p.alpha, q + 4);
+          if (sl < nslab) {
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32b_x32(taddr + sl * 64, r0);
+            tmem_ld_32x32b_x32(taddr + sl * 64 + 32, r1);
+            tmem_ld_wait();
+            if (sl == nslab - 1) release();
+            uint4 q[8];
+            if constexpr (EPI == EPI_BF16_ROPE) {
+              rope32_bf16(r0, cs, rot, p.alpha, q);
+              rope32_bf16(r1, cs + 8, rot, p.alpha, q + 4);
+            } else {
+              pack32_bf16(r0, p.alpha, q);
+              pack32_bf16(r1, p.alpha, q + 4);
+            }
+            if (n0 + sl * 64 < p.N) put(&tma_c, q, n0 + sl * 64, row0);
           }
-          if (n0 + sl * 64 < p.N) put(&tma_c, q, n0 + sl * 64, row0);
         }
       } else {  // fp32 store / fp32 reduce-add: boxes of 32 columns
-        const int n0 = n_blk * BN + hh * 128;
+        const int n0 = n_blk * BN + wk.ncol0 + tcol;
         mbar_wait(tmem_full_bar(acc), acc_phase);
         tc_fence_after();
 #pragma unroll
         for (int sl = 0; sl < 4; ++sl) {
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(taddr + sl * 32, r);
-          tmem_ld_wait();
-          if (sl == 3) release();
-          uint4 q[8];
-          pack32_f32(r, p.alpha, q);
-          if (n0 + sl * 32 < p.N) put(&tma_c, q, n0 + sl * 32, row0);
+          if (sl < 2 * nslab) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + sl * 32, r);
+            tmem_ld_wait();
+            if (sl == 2 * nslab - 1) release();
+            uint4 q[8];
+            pack32_f32(r, p.alpha, q);
+            if (n0 + sl * 32 < p.N) put(&tma_c, q, n0 + sl * 32, row0);
+          }
         }
       }
     }
@@ -848,6 +887,7 @@ static int dispatch_major(int a_mn, int b_mn, int epi, const CUtensorMap& ta, co
 // du half, x = h of the fused SwiGLU forward.  Unused ones repeat c.
 struct PairOut {
   CUtensorMap c, c2, x;
+  CUtensorMap bn;  // B with a 64-row box (K-major B, halved tail tiles); repeats tb when unused
 };
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -860,7 +900,7 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_set = true;
   }
-  kern<<<grid, kPairThreads, PairCfg::kSmemBytes, st>>>(ta, tb, o.c, o.c2, o.x, p);  // __cluster_dims__(2,1,1): grid is even
+  kern<<<grid, kPairThreads, PairCfg::kSmemBytes, st>>>(ta, tb, o.bn, o.c, o.c2, o.x, p);  // __cluster_dims__(2,1,1): grid is even
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
 }
@@ -913,12 +953,14 @@ static int auto_splits(int M, int N, int K) {
 }
 
 static int g_gemm_mode = 0;  // 0 auto, 1 single-CTA tiles only, 2 CTA-pair tiles whenever legal
+static int g_gemm_tail = 1;  // halve the tiles of a sparse last wave (pcv_gemm_set_mode(3 / 4) turns it off / on)
 
 }  // namespace pcv
 
 extern "C" int pcv_gemm_set_mode(int mode) {
-  if (mode < 0 || mode > 2) return PCV_ERR_ARG;
-  pcv::g_gemm_mode = mode;
+  if (mode < 0 || mode > 4) return PCV_ERR_ARG;
+  if (mode >= 3) pcv::g_gemm_tail = mode == 4;
+  else pcv::g_gemm_mode = mode;
   return PCV_OK;
 }
 
@@ -965,6 +1007,22 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       if (rc) return rc;
       o.c2 = o.c;
       o.x = o.c;
+      o.bn = tb;
+      // tail of the schedule: if the last wave would occupy at most half of the pairs, run its tiles as 256 x 128 halves
+      p.full_tiles = static_cast<int>(t2);
+      p.narrow = 0;
+      {
+        const long np = num_sms() / 2;
+        const long rem = t2 % np;
+        if (g_gemm_tail && sp == 1 && epilogue != PCV_EPI_F32_ATOMIC && t2 > np && rem > 0 && 2 * rem <= np) {
+          p.full_tiles = static_cast<int>(t2 - rem);
+          p.narrow = 1;
+          if (!b_mn_major) {
+            rc = get_tmap_2d_bf16(&o.bn, B, N, K, ldb, 64);
+            if (rc) return rc;
+          }
+        }
+      }
       const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
       count_launch();
       return dispatch_major_pair(a_mn_major, b_mn_major, epilogue, ta, tb, o, p, static_cast<int>(2 * pairs), st);
@@ -1050,6 +1108,9 @@ static int gemm_swiglu_impl(bool bwd, const void* A, const void* W, void* C, voi
   if (!bwd) rc = get_tmap_2d_bf16(&o.x, aux, M, hid, ld_aux, 32);
   else o.x = o.c;
   if (rc) return rc;
+  o.bn = tb;
+  p.full_tiles = p.m_tiles * p.n_tiles;
+  p.narrow = 0;
   const long t2 = static_cast<long>(p.m_tiles) * p.n_tiles;
   const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
   count_launch();

@@ -9,6 +9,7 @@ Reference operations replaced (see include/plaincv_b200.h for the per-kernel cit
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -211,6 +212,44 @@ def rope_table(head_dim: int, seq_len: int, theta: float, device) -> torch.Tenso
     return torch.stack([torch.cos(freqs), torch.sin(freqs)], dim=-1).contiguous().to(device)
 
 
+# ------------------------------------------------------------------------------------------------ side stream
+class _WgradStream:
+    """Weight-gradient GEMMs feed nothing downstream in a block's backward, so they are launched on a second stream:
+    when the dgrad GEMM on the main stream runs its last, partial wave of tiles, the idle SMs pick up the wgrad
+    kernel's CTAs instead of waiting (both kernels are persistent, one CTA per SM).  `launch` orders the wgrad after
+    everything already queued on the main stream; `join` makes the main stream wait for all of them (called before
+    the gradients are handed to the reducer / the caller).  Tensors passed to `launch` are kept alive until `join`."""
+
+    def __init__(self):
+        self.streams = {}
+        self.keep = []
+        self.enabled = os.environ.get("PCV_WGRAD_STREAM", "1") != "0"  # 0: same-stream launches (A/B measurements)
+
+    def _side(self, dev) -> "torch.cuda.Stream":
+        st = self.streams.get(dev)
+        if st is None:
+            st = self.streams[dev] = torch.cuda.Stream(device=dev)
+        return st
+
+    def launch(self, x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, alpha: float = 1.0) -> None:
+        if not self.enabled:
+            linear_wgrad(x, dy, dw, alpha)
+            return
+        side = self._side(x.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            linear_wgrad(x, dy, dw, alpha)
+        self.keep.append((x, dy))
+
+    def join(self, dev) -> None:
+        if self.keep:
+            torch.cuda.current_stream().wait_stream(self._side(dev))
+            self.keep.clear()
+
+
+wgrad_stream = _WgradStream()
+
+
 # ------------------------------------------------------------------------------------------------ autograd: per op
 class LinearFn(torch.autograd.Function):
     """y = x @ W for a flax (in,out) kernel.  `w_bf16` is the padded bf16 copy [K, Np]; the weight gradient is
@@ -343,22 +382,24 @@ class BlockFn(torch.autograd.Function):
         layer, rt = ctx.layer, ctx.rt
         d_m = d_m.contiguous()
         # MLP branch
+        wg = wgrad_stream
+        wg.launch(hh, d_m, layer.g_down)
         d_gu = linear_dgrad_dswiglu(d_m, layer.w_down, gu)
-        linear_wgrad(hh, d_m, layer.g_down)
+        wg.launch(h2, d_gu, layer.g_gu)
         d_h2 = linear_dgrad(d_gu, layer.w_gu)
-        linear_wgrad(h2, d_gu, layer.g_gu)
         del d_gu
         d_r2 = rmsnorm_residual_bwd(d_h2, d_res2, res2, layer.mlp_norm, rstd2, layer.g_mlp_norm)
         del d_h2
         # attention branch
+        wg.launch(o, d_r2, layer.g_out)
         d_o = linear_dgrad(d_r2, layer.w_out)
-        linear_wgrad(o, d_r2, layer.g_out)
         d_qkv = attn_bwd(qkv, rt.cos_sin, rt.doc_start, o, d_o, lse, rt.B, rt.T, rt.n_heads)
         del d_o
+        wg.launch(h1, d_qkv, layer.g_qkv)
         d_h1 = linear_dgrad(d_qkv, layer.w_qkv)
-        linear_wgrad(h1, d_qkv, layer.g_qkv)
         del d_qkv
         d_r1 = rmsnorm_residual_bwd(d_h1, d_r2, res1, layer.attn_norm, rstd1, layer.g_attn_norm)
+        wg.join(d_r1.device)
         if layer.on_grads_ready is not None:
             layer.on_grads_ready()
         return d_r1, (d_r1 if ctx.has_delta else None), None, None
@@ -386,9 +427,10 @@ class HeadLossFn(torch.autograd.Function):
         res_f, rstd, hf, dlogits = ctx.saved_tensors
         head = ctx.head
         alpha = 1.0 if ctx.unit_grad else float(g_out[0])
+        wgrad_stream.launch(hf, dlogits, head.g_lm, alpha)
         d_hf = linear_dgrad(dlogits, head.w_lm, alpha)
-        linear_wgrad(hf, dlogits, head.g_lm, alpha)
         d_r = rmsnorm_residual_bwd(d_hf, None, res_f, head.out_norm, rstd, head.g_out_norm)
+        wgrad_stream.join(d_r.device)
         if head.on_grads_ready is not None:
             head.on_grads_ready()
         return d_r, (d_r if ctx.has_delta else None), None, None, None, None, None
