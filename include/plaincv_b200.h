@@ -44,6 +44,10 @@ int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
 /* Tiling override for tests and benchmarks: 0 = automatic (CTA-pair 256x256 tiles, tcgen05 cta_group::2, whenever they
  * fill the machine; single-CTA 128xBN tiles otherwise), 1 = single-CTA tiles only, 2 = CTA-pair tiles always. */
 int pcv_gemm_set_mode(int mode);
+/* Measurement hook: when dev_buf is non-null the epilogue warps of the CTA-pair GEMMs write, per (CTA, epilogue warp),
+ * 8 uint32: cycles waiting for the accumulator, waiting for epilogue operands, in the math, in the stores, total.
+ * dev_buf holds grid x 8 x 8 uint32 (grid <= number of SMs); null switches it off. */
+int pcv_gemm_set_profile(void* dev_buf);
 
 /* fp32 master -> bf16 compute copy, zero-filling the padded tail columns: dst[rows][dst_ld] <- src[rows][src_ld][:cols].
  * Replaces flax's per-call promote_dtype of `kernel`/`embedding` (transformer.py: every nn.Dense / nn.Embed). */

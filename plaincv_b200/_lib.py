@@ -31,6 +31,7 @@ SIGNATURES = {
     "pcv_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                               c_int, c_int, c_float, c_void_p]),
     "pcv_gemm_set_mode": (c_int, [c_int]),
+    "pcv_gemm_set_profile": (c_int, [c_void_p]),
     "pcv_cast_pad_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "pcv_embed_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pcv_embed_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
@@ -84,6 +85,8 @@ def load() -> ctypes.CDLL:
         lib.pcv_gemm_set_mode(int(os.environ["PCV_GEMM_MODE"]))
     if "PCV_GEMM_TAIL" in os.environ:
         lib.pcv_gemm_set_mode(4 if os.environ["PCV_GEMM_TAIL"] != "0" else 3)
+    if "PCV_GEMM_DBG" in os.environ:
+        lib.pcv_gemm_set_mode(100 + int(os.environ["PCV_GEMM_DBG"]))
     _lib = lib
     return lib
 

@@ -521,6 +521,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t bdQempty = sBar + 8u * 11;                     // (128)
   const uint32_t bAccFull = sBar + 8u * 12;                     // (1, commit) dK/dV complete
   const uint32_t tmem_ptr_smem = sBar + 8u * 13;
+  const uint32_t bSdPfree = sBar + 8u * 14;                     // (256) S / dP of a tile are in registers
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -559,6 +560,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
     mbar_init(bSdPfull, 1);
     mbar_init(bPdSfull, 256);
+    mbar_init(bSdPfree, 256);
     mbar_init(bdQfull, 1);
     mbar_init(bdQempty, 128);
     mbar_init(bAccFull, 1);
@@ -627,18 +629,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const int stage = it % 3;
         const uint32_t sPb = sP, sdSb = sdS;
         TRACE(4, it * 2 + 0);
-        mbar_wait(bPdSfull, it & 1);  // P/dS(it) are in shared memory; S/dP in TMEM have been consumed
-        tc_fence_after();
-        TRACE(4, it * 2 + 1);
-        // next tile's S and dP first: they are what the compute warps wait for
+        // next tile's S and dP first: they are what the compute warps wait for.  They may overwrite S / dP as soon as
+        // every compute thread holds its part of tile `it` in registers — about half of that tile's math still to go,
+        // which is what hides the latency of these MMAs
         if (it + 1 < n_it) {
           const int s1 = (it + 1) % 3;
           mbar_wait(bQdOfull(s1), ((it + 1) / 3) & 1);
+          mbar_wait(bSdPfree, it & 1);
           tc_fence_after();
           TRACE(5, it * 4 + 0);
           issue_SdP(s1);
           TRACE(5, it * 4 + 1);
         }
+        mbar_wait(bPdSfull, it & 1);  // P/dS(it) are in shared memory and tensor memory
+        tc_fence_after();
+        TRACE(4, it * 2 + 1);
         mbar_wait(bdQempty, (it & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
         tc_fence_after();
         TRACE(5, it * 4 + 2);
@@ -732,6 +737,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tmem_ld_32x32b_x32(tS + lane_off + col0, sr);
         tmem_ld_32x32b_x32(tdP + lane_off + col0, pr);
         tmem_ld_wait();
+        if (c == 1) {  // this thread's share of S and dP has left tensor memory
+          tc_fence_before();
+          mbar_arrive(bSdPfree);
+        }
         if (need_mask) chunk_p_ds<true>(sr, pr, c2, lse2, dlt_s, ds_t - key0 - col0, t - key0 - col0, pk_p[c], pk_ds[c]);
         else chunk_p_ds<false>(sr, pr, c2, lse2, dlt_s, 0, 0, pk_p[c], pk_ds[c]);
       }

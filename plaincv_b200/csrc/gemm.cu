@@ -59,6 +59,8 @@ struct GemmParams {
   // CTA-pair kernel, tail of the persistent schedule: the tiles of the last, partial wave (index >= full_tiles) are cut
   // into two 256 x 128 halves when that lets every pair work on it (narrow = 1), instead of leaving pairs idle
   int full_tiles, narrow;
+  unsigned int* prof;  // measurement only (pcv_gemm_set_profile): per epilogue warp, cycles spent per phase
+  int dbg;  // measurement only (pcv_gemm_set_mode(100 + flags)): leave out parts of the fused epilogues
 };
 constexpr int EPI_BF16_ROPE = 3;  // internal: PCV_EPI_BF16 + RoPE (pcv_gemm_bf16_rope)
 constexpr int EPI_SWIGLU = 4;     // internal: [g | u] = X W_gu written to C, h = silu(g) * u written to aux
@@ -81,6 +83,12 @@ __device__ __forceinline__ void decode_work(const GemmParams& p, int w, int& m_b
   n_blk = r / gm;
 }
 
+
+__device__ __forceinline__ unsigned int clk32() {
+  unsigned int c;
+  asm volatile("mov.u32 %0, %%clock;" : "=r"(c));
+  return c;
+}
 
 // CTA-pair schedule: work index -> tile, k split and (for the halved tail tiles) which 128-column half.
 struct PairWork {
@@ -416,20 +424,29 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 //   accumulate into both CTAs' tensor memory (128 lanes each); each CTA's epilogue warps drain their own half.
 // Per k-block a CTA pulls 32 KB for 2*128*256*64 flop: 128 flop per L2 byte against 85 for the single-CTA
 // 128 x 256 tile — the single-CTA kernel saturates the L2 -> SM fabric (~12 TB/s) near 1.1 PFLOP/s.
-struct PairCfg {
+constexpr bool pair_epi_fused(int epi) { return epi == EPI_SWIGLU || epi == EPI_DSWIGLU; }
+template <int EPI>
+struct PairCfgT {
+  static constexpr bool kFused = pair_epi_fused(EPI);  // SwiGLU forward / backward in the epilogue
   static constexpr int kBN = 256;
   static constexpr int kTileM = 256;
-  static constexpr int kStages = 6;
+  // the fused epilogues trade one pipeline stage for a second 4 KB box per epilogue warp (two stores in flight, or the
+  // saved gate and up slabs of the SwiGLU backward brought in by TMA while the previous slab is still being worked on)
+  static constexpr int kStages = kFused ? 5 : 6;
   static constexpr int kABytes = 128 * kBK * 2;  // this CTA's 128 rows of A
   static constexpr int kBBytes = 128 * kBK * 2;  // this CTA's 128 of the 256 B rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarBytes = 256;
   static constexpr int kEpiWarps = 8;
-  static constexpr int kEpiBufBytes = 32 * 128;  // per epilogue warp: 32 rows x 128 B (one 128B-swizzled TMA box)
+  static constexpr int kEpiBoxBytes = 32 * 128;  // 32 rows x 128 B (one 128B-swizzled TMA box)
+  static constexpr int kEpiBoxes = kFused ? 2 : 1;
+  static constexpr int kEpiBufBytes = kEpiBoxes * kEpiBoxBytes;  // per epilogue warp
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + kBarBytes + 1024;
   static constexpr uint32_t kTmemCols = 512;  // two 256-column accumulators
 };
-static_assert(PairCfg::kSmemBytes <= 232448, "CTA-pair GEMM shared memory exceeds 227 KB");
+using PairCfg = PairCfgT<0>;
+static_assert(PairCfgT<0>::kSmemBytes <= 232448 && PairCfgT<EPI_SWIGLU>::kSmemBytes <= 232448,
+              "CTA-pair GEMM shared memory exceeds 227 KB");
 
 template <bool A_MN, bool B_MN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
@@ -437,7 +454,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
                       const __grid_constant__ CUtensorMap tma_bn, const __grid_constant__ CUtensorMap tma_c,
                       const __grid_constant__ CUtensorMap tma_c2, const __grid_constant__ CUtensorMap tma_x,
                       const GemmParams p) {
-  using Cfg = PairCfg;
+  using Cfg = PairCfgT<EPI>;
   constexpr int BN = Cfg::kBN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -475,6 +492,9 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);   // multicast tcgen05.commit
       mbar_init(tmem_empty_bar(s), 16);  // leader: 8 epilogue warps of each CTA
+    }
+    if constexpr (EPI == EPI_DSWIGLU) {  // one per epilogue warp: its gate / up slab has landed
+      for (int s = 0; s < Cfg::kEpiWarps; ++s) mbar_init(bar_base + 8u * (2 * Cfg::kStages + 5 + s), 1);
     }
     fence_mbar_init();
   }
@@ -577,21 +597,137 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     const int ew = warp & 3;
     const int hh = (warp - 4) >> 2;
     const uint32_t buf = smem_epi + static_cast<uint32_t>(warp - 4) * Cfg::kEpiBufBytes;
-    const uint32_t my_row = buf + lane * 128;
     const uint32_t sw = lane & 7;
+    // with two boxes per warp (fused SwiGLU forward) consecutive puts alternate between them: a box is rewritten only
+    // once the store issued two puts earlier has read it, so one store is always in flight behind the math
+    uint32_t put_box = 0;
+    unsigned int pf0 = 0, pf1 = 0, pf2 = 0, pf3 = 0, pt = 0;  // profile: wait accumulator | wait operands | math | stores
+    const bool prof = p.prof != nullptr;
+    const unsigned int pstart = clk32();
     auto put = [&](const CUtensorMap* m, const uint4* q, int c0, int r0) {
-      if (lane == 0) tma_store_wait_read<0>();  // the previous box has been read out of the buffer
+      if (p.dbg & 1) return;
+      const uint32_t bx = buf + put_box * Cfg::kEpiBoxBytes;
+      if (lane == 0) tma_store_wait_read<Cfg::kEpiBoxes - 1>();  // the store that last used this box has read it
       __syncwarp();
 #pragma unroll
-      for (int v = 0; v < 8; ++v) st_shared_v4(my_row + ((v ^ sw) << 4), q[v]);
+      for (int v = 0; v < 8; ++v) st_shared_v4(bx + lane * 128 + ((v ^ sw) << 4), q[v]);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        if constexpr (EPI == PCV_EPI_F32_ATOMIC) tma_reduce_add_2d(m, buf, c0, r0);
-        else tma_store_2d(m, buf, c0, r0);
+        if constexpr (EPI == PCV_EPI_F32_ATOMIC) tma_reduce_add_2d(m, bx, c0, r0);
+        else tma_store_2d(m, bx, c0, r0);
         tma_store_commit();
       }
+      if constexpr (Cfg::kEpiBoxes == 2) put_box ^= 1u;
     };
+    if constexpr (EPI == EPI_DSWIGLU) {
+      // SwiGLU backward in the epilogue of the fc2 dgrad GEMM.  Per warp and tile: two slabs of 32 rows x 64 columns.
+      // The saved gate and up values of a slab arrive by TMA in the warp's two boxes (requested as soon as the previous
+      // slab's stores have read the boxes, i.e. while the MMAs of this tile still run), every lane reads its own row,
+      // turns (dh, g, u) into (dg, du) in place and the two boxes leave again by TMA store.
+      const uint32_t box_g = buf, box_u = buf + Cfg::kEpiBoxBytes;
+      const uint32_t row_g = box_g + lane * 128, row_u = box_u + lane * 128;
+      const uint32_t ld_bar = bar_base + 8u * (2 * Cfg::kStages + 5 + (warp - 4));
+      uint32_t ld_phase = 0;
+      // slab (w, sl) of this warp: first column / first row, and whether any of it lies inside the matrix
+      auto coords = [&](int w, int sl, int& c, int& r) -> bool {
+        const PairWork wk = decode_pair_work(p, w);
+        r = wk.m_blk * Cfg::kTileM + static_cast<int>(rank) * 128 + ew * 32;
+        c = wk.n_blk * BN + hh * 128 + sl * 64;
+        return c < p.N && r < p.M;
+      };
+      auto seek = [&](int& w, int& sl, int& c, int& r) -> bool {  // first slab at or after (w, sl) that exists
+        while (w < total_work) {
+          if (coords(w, sl, c, r)) return true;
+          if (sl == 0) sl = 1;
+          else { sl = 0; w += npairs; }
+        }
+        return false;
+      };
+      auto request = [&](int c, int r) {  // lane 0
+        if (p.dbg & 8) return;
+        mbar_expect_tx(ld_bar, 2 * Cfg::kEpiBoxBytes);
+        tma_load_2d(box_g, &tma_x, ld_bar, c, r);
+        tma_load_2d(box_u, &tma_bn, ld_bar, c, r);
+      };
+      int nw = pair, nsl = 0, nc = 0, nr = 0;  // the slab whose gate / up values are on their way
+      if (seek(nw, nsl, nc, nr) && lane == 0) request(nc, nr);
+      int it = 0;
+      for (int w = pair; w < total_work; w += npairs, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + hh * 128;
+        int c0, c1, row0;
+        const bool has0 = coords(w, 0, c0, row0);
+        const bool has1 = coords(w, 1, c1, row0);
+        if (prof) pt = clk32();
+        mbar_wait(tmem_full_bar(acc), acc_phase);
+        tc_fence_after();
+        if (prof) { const unsigned int t = clk32(); pf0 += t - pt; pt = t; }
+        auto release = [&]() {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_shared(tmem_empty_bar(acc), 0));
+        };
+        if (!has0 && !has1) release();
+#pragma unroll
+        for (int sl = 0; sl < 2; ++sl) {
+          if (sl == 0 ? !has0 : !has1) continue;
+          const bool last = (sl == 1) || !has1;
+          uint4 pg[8], pu[8];
+          if (!(p.dbg & 8)) {
+            mbar_wait(ld_bar, ld_phase);
+            ld_phase ^= 1u;
+          }
+          if (prof) { const unsigned int t = clk32(); pf1 += t - pt; pt = t; }
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            pg[v] = ld_shared_v4(row_g + ((v ^ sw) << 4));
+            pu[v] = ld_shared_v4(row_u + ((v ^ sw) << 4));
+          }
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(taddr + sl * 64 + half * 32, r);
+            tmem_ld_wait();
+            if (last && half == 1) release();
+            if (p.dbg & 4) {
+              pack32_bf16(r, p.alpha, pg + 4 * half);
+              pack32_bf16(r, 2.f, pu + 4 * half);
+            } else {
+              dswiglu32(r, p.alpha, pg + 4 * half, pu + 4 * half);
+            }
+          }
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            st_shared_v4(row_g + ((v ^ sw) << 4), pg[v]);
+            st_shared_v4(row_u + ((v ^ sw) << 4), pu[v]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (prof) { const unsigned int t = clk32(); pf2 += t - pt; pt = t; }
+          // the slab after this one
+          nw = w;
+          nsl = sl;
+          if (nsl == 0) nsl = 1;
+          else { nsl = 0; nw += npairs; }
+          const bool more = seek(nw, nsl, nc, nr);
+          if (lane == 0) {
+            if (!(p.dbg & 1)) {
+              tma_store_2d(&tma_c, box_g, sl == 0 ? c0 : c1, row0);
+              tma_store_2d(&tma_c2, box_u, sl == 0 ? c0 : c1, row0);
+              tma_store_commit();
+            }
+            if (more) {
+              tma_store_wait_read<0>();  // both boxes have been read by the stores: they can take the next slab
+              request(nc, nr);
+            }
+          }
+          __syncwarp();
+          if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
+        }
+      }
+    } else {
     int it = 0;
     for (int w = pair; w < total_work; w += npairs, ++it) {
       const PairWork wk = decode_pair_work(p, w);
@@ -612,8 +748,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         // accumulator columns [0,128) = gate, [128,256) = up of hidden units [n_blk*128, +128); this warp: 64 of them
         const int n0 = n_blk * 128 + hh * 64;
         const uint32_t tg = taddr - tcol + hh * 64;
+        if (prof) pt = clk32();
         mbar_wait(tmem_full_bar(acc), acc_phase);
         tc_fence_after();
+        if (prof) { const unsigned int t = clk32(); pf0 += t - pt; pt = t; }
         uint4 qg[8], qu[8], qh[8];
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
@@ -622,64 +760,21 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           tmem_ld_32x32b_x32(tg + 128 + c * 32, u);
           tmem_ld_wait();
           if (c == 1) release();
-          swiglu32(g, u, qg + 4 * c, qu + 4 * c, qh + 4 * c);
+          if (p.dbg & 4) {
+            pack32_bf16(g, 1.f, qg + 4 * c);
+            pack32_bf16(u, 1.f, qu + 4 * c);
+            pack32_bf16(u, 2.f, qh + 4 * c);
+          } else {
+            swiglu32(g, u, qg + 4 * c, qu + 4 * c, qh + 4 * c);
+          }
         }
+        if (prof) { const unsigned int t = clk32(); pf2 += t - pt; pt = t; }
         if (n0 < p.N) {
           put(&tma_c, qg, n0, row0);
           put(&tma_c2, qu, n0, row0);
-          put(&tma_x, qh, n0, row0);
+          if (!(p.dbg & 2)) put(&tma_x, qh, n0, row0);
         }
-      } else if constexpr (EPI == EPI_DSWIGLU) {
-        const int n0 = n_blk * BN + hh * 128;
-        const __nv_bfloat16* gu = reinterpret_cast<const __nv_bfloat16*>(p.aux);
-        uint4 pg[8], pu[8];
-        // coalesced fetch of a 32-row x 64-column slab of g and of u: lane -> (row 4i + lane/8, 16-byte piece lane%8)
-        auto fetch = [&](int c0) {
-          const int c = c0 + (lane & 7) * 8;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = row0 + 4 * i + (lane >> 3);
-            const bool ok = r < p.M && c + 8 <= p.N;
-            const __nv_bfloat16* src = gu + static_cast<size_t>(r) * p.ld_aux + c;
-            pg[i] = ok ? __ldg(reinterpret_cast<const uint4*>(src)) : make_uint4(0, 0, 0, 0);
-            pu[i] = ok ? __ldg(reinterpret_cast<const uint4*>(src + p.half_off)) : make_uint4(0, 0, 0, 0);
-          }
-        };
-        // pieces -> through the staging box -> this lane's own row (8 pieces = 64 columns)
-        auto transpose = [&](uint4* pcs) {
-          if (lane == 0) tma_store_wait_read<0>();
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const uint32_t rr = 4 * i + (lane >> 3);
-            st_shared_v4(buf + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4), pcs[i]);
-          }
-          __syncwarp();
-#pragma unroll
-          for (int v = 0; v < 8; ++v) pcs[v] = ld_shared_v4(my_row + ((v ^ sw) << 4));
-          __syncwarp();
-        };
-        fetch(n0);  // gu is an input of the launch: fetched while the MMAs of this tile still run
-        mbar_wait(tmem_full_bar(acc), acc_phase);
-        tc_fence_after();
-#pragma unroll
-        for (int sl = 0; sl < 2; ++sl) {
-          transpose(pg);
-          transpose(pu);
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint32_t r[32];
-            tmem_ld_32x32b_x32(taddr + sl * 64 + half * 32, r);
-            tmem_ld_wait();
-            if (sl == 1 && half == 1) release();
-            dswiglu32(r, p.alpha, pg + 4 * half, pu + 4 * half);
-          }
-          if (n0 + sl * 64 < p.N) {
-            put(&tma_c, pg, n0 + sl * 64, row0);
-            put(&tma_c2, pu, n0 + sl * 64, row0);
-          }
-          if (sl == 0) fetch(n0 + 64);
-        }
+        if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
       } else if constexpr (EPI == EPI_BF16_ROPE || EPI == PCV_EPI_BF16) {
         const int n0 = n_blk * BN + wk.ncol0 + tcol;
         // (cos, sin) of this row's position for the 32 pairs of a head: the same for every head of the tile, so they
@@ -694,8 +789,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             for (int v = 0; v < 16; ++v) cs[v] = __ldg(src + v);
           }
         }
+        if (prof) pt = clk32();
         mbar_wait(tmem_full_bar(acc), acc_phase);
         tc_fence_after();
+        if (prof) { const unsigned int t = clk32(); pf0 += t - pt; pt = t; }
 #pragma unroll
         for (int sl = 0; sl < 2; ++sl) {
           if (sl < nslab) {
@@ -712,7 +809,9 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
               pack32_bf16(r0, p.alpha, q);
               pack32_bf16(r1, p.alpha, q + 4);
             }
+            if (prof) { const unsigned int t = clk32(); pf2 += t - pt; pt = t; }
             if (n0 + sl * 64 < p.N) put(&tma_c, q, n0 + sl * 64, row0);
+            if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
           }
         }
       } else {  // fp32 store / fp32 reduce-add: boxes of 32 columns
@@ -732,6 +831,11 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           }
         }
       }
+    }
+    }  // EPI != EPI_DSWIGLU
+    if (prof && lane == 0) {
+      unsigned int* dst = p.prof + (static_cast<size_t>(blockIdx.x) * 8 + (warp - 4)) * 8;
+      dst[0] = pf0; dst[1] = pf1; dst[2] = pf2; dst[3] = pf3; dst[4] = clk32() - pstart;
     }
     if (lane == 0) tma_store_wait<0>();  // every box has left shared memory and reached global memory
     __syncwarp();
@@ -896,11 +1000,11 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
   auto kern = gemm_bf16_pair_kernel<A_MN, B_MN, EPI>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfgT<EPI>::kSmemBytes);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_set = true;
   }
-  kern<<<grid, kPairThreads, PairCfg::kSmemBytes, st>>>(ta, tb, o.bn, o.c, o.c2, o.x, p);  // __cluster_dims__(2,1,1): grid is even
+  kern<<<grid, kPairThreads, PairCfgT<EPI>::kSmemBytes, st>>>(ta, tb, o.bn, o.c, o.c2, o.x, p);  // __cluster_dims__(2,1,1): grid is even
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
 }
@@ -953,11 +1057,19 @@ static int auto_splits(int M, int N, int K) {
 }
 
 static int g_gemm_mode = 0;  // 0 auto, 1 single-CTA tiles only, 2 CTA-pair tiles whenever legal
+static int g_gemm_dbg = 0;
+static unsigned int* g_gemm_prof = nullptr;
 static int g_gemm_tail = 1;  // halve the tiles of a sparse last wave (pcv_gemm_set_mode(3 / 4) turns it off / on)
 
 }  // namespace pcv
 
+extern "C" int pcv_gemm_set_profile(void* dev_buf) {
+  pcv::g_gemm_prof = static_cast<unsigned int*>(dev_buf);
+  return PCV_OK;
+}
+
 extern "C" int pcv_gemm_set_mode(int mode) {
+  if (mode >= 100 && mode < 164) { pcv::g_gemm_dbg = mode - 100; return PCV_OK; }
   if (mode < 0 || mode > 4) return PCV_ERR_ARG;
   if (mode >= 3) pcv::g_gemm_tail = mode == 4;
   else pcv::g_gemm_mode = mode;
@@ -1011,6 +1123,8 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       // tail of the schedule: if the last wave would occupy at most half of the pairs, run its tiles as 256 x 128 halves
       p.full_tiles = static_cast<int>(t2);
       p.narrow = 0;
+      p.dbg = g_gemm_dbg;
+      p.prof = g_gemm_prof;
       {
         const long np = num_sms() / 2;
         const long rem = t2 % np;
@@ -1105,12 +1219,16 @@ static int gemm_swiglu_impl(bool bwd, const void* A, const void* W, void* C, voi
   if (rc) return rc;
   rc = get_tmap_2d_bf16(&o.c2, cb + hid, M, hid, ldc, 32);
   if (rc) return rc;
-  if (!bwd) rc = get_tmap_2d_bf16(&o.x, aux, M, hid, ld_aux, 32);
-  else o.x = o.c;
+  // forward: x = h (output).  backward: x / bn = the gate / up half of the saved gu (inputs of the epilogue)
+  rc = get_tmap_2d_bf16(&o.x, aux, M, hid, ld_aux, 32);
   if (rc) return rc;
-  o.bn = tb;
+  if (bwd) rc = get_tmap_2d_bf16(&o.bn, static_cast<__nv_bfloat16*>(aux) + hid, M, hid, ld_aux, 32);
+  else o.bn = tb;
+  if (rc) return rc;
   p.full_tiles = p.m_tiles * p.n_tiles;
   p.narrow = 0;
+  p.dbg = g_gemm_dbg;
+  p.prof = g_gemm_prof;
   const long t2 = static_cast<long>(p.m_tiles) * p.n_tiles;
   const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
   count_launch();

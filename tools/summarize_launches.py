@@ -1,6 +1,10 @@
 #!/usr/bin/env python
 """Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list by kernel name.
-usage: python tools/summarize_launches.py gpurun_out/launches.csv [first_id last_id]"""
+usage: python tools/summarize_launches.py gpurun_out/launches.csv [first_id last_id]
+       python tools/summarize_launches.py gpurun_out/launches.csv --step K
+--step K keeps exactly the K-th (0-based) training step of the capture: from the gradient zero-fill / bf16 weight
+refresh in front of the K-th embed_fwd launch up to that step's embed_bwd (the last kernel of backward), so that the
+per-kernel shares are those of one bench.py step and exclude the bench's separate GEMM replay."""
 import csv
 import re
 import sys
@@ -9,8 +13,13 @@ from collections import defaultdict
 
 def main():
     path = sys.argv[1]
-    lo = int(sys.argv[2]) if len(sys.argv) > 2 else 0
-    hi = int(sys.argv[3]) if len(sys.argv) > 3 else 1 << 60
+    step = None
+    if len(sys.argv) > 3 and sys.argv[2] == "--step":
+        step = int(sys.argv[3])
+        lo, hi = 0, 1 << 60
+    else:
+        lo = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+        hi = int(sys.argv[3]) if len(sys.argv) > 3 else 1 << 60
     rows = []
     with open(path, newline="") as f:
         lines = [l for l in f if not l.startswith("==")]
@@ -27,6 +36,13 @@ def main():
         name = re.sub(r"\(.*", "", r["Kernel Name"])
         name = re.sub(r"<.*", "", name)
         rows.append((i, name, ns))
+    if step is not None:
+        fwd = [k for k, r in enumerate(rows) if "embed_fwd" in r[1]]
+        k0 = fwd[step]
+        while k0 > 0 and ("cast_pad" in rows[k0 - 1][1] or "at::" in rows[k0 - 1][1]):
+            k0 -= 1
+        k1 = next(k for k in range(fwd[step], len(rows)) if "embed_bwd" in rows[k][1])
+        rows = rows[k0:k1 + 1]
     agg = defaultdict(lambda: [0, 0.0])
     for _, n, ns in rows:
         agg[n][0] += 1
