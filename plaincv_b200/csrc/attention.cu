@@ -34,6 +34,12 @@ namespace pcv {
 #ifdef PCV_TRACE
 // Debug-only timeline (clock64 at phase boundaries of CTA (0,0,0)); compiled in with -DPCV_TRACE, never in the product build.
 __device__ long long g_trace[8192];
+__device__ long long g_cta_trace[4096 * 4];  // per backward CTA: globaltimer at entry / exit, SM id, iterations
+__device__ __forceinline__ long long gtimer() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 #define TRACE(slot, idx) do { if (trace_on && (idx) < 1024) g_trace[(slot) * 1024 + (idx)] = clock64(); } while (0)
 #else
 #define TRACE(slot, idx) do { } while (0)
@@ -52,6 +58,11 @@ __device__ __forceinline__ float ex2f(float x) {
 }
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
 }
 __device__ __forceinline__ uint4 ld_global_nc_v4(const void* p) {
   uint4 v;
@@ -504,7 +515,8 @@ __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.syn
 
 __global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                const __grid_constant__ CUtensorMap tm_dq, const float* __restrict__ cos_sin,
+                const __grid_constant__ CUtensorMap tm_dq, const __grid_constant__ CUtensorMap tm_cs,
+                const __grid_constant__ CUtensorMap tm_dqkv, const float* __restrict__ cos_sin,
                 const int32_t* __restrict__ doc_start, const float* __restrict__ lse, const float* __restrict__ delta,
                 float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
@@ -522,12 +534,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t bAccFull = sBar + 8u * 12;                     // (1, commit) dK/dV complete
   const uint32_t tmem_ptr_smem = sBar + 8u * 13;
   const uint32_t bSdPfree = sBar + 8u * 14;                     // (256) S / dP of a tile are in registers
+  const uint32_t bPfree = sBar + 8u * 15;                       // (1, commit) dV MMAs done: P in shared memory is free
+  const uint32_t bCSfull = sBar + 8u * 16;                      // (tx) rotation table rows of the key tile
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef PCV_TRACE
   const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 416);
+  const int cta_lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (tid == 0 && cta_lin < 4096) {
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_cta_trace[cta_lin * 4 + 0] = gtimer();
+    g_cta_trace[cta_lin * 4 + 2] = smid;
+  }
 #endif
+  TRACE(6, 5);
   const int j = blockIdx.x;  // key tile
   const int h = blockIdx.y, b = blockIdx.z;
   const int d = NH * 64, ld = 3 * d;
@@ -553,6 +575,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     tma_prefetch_desc(&tm_dq);
+    tma_prefetch_desc(&tm_cs);
+    tma_prefetch_desc(&tm_dqkv);
     mbar_init(bKVfull, 1);
     for (int s = 0; s < AttnBwdSmem::kStages; ++s) {
       mbar_init(bQdOfull(s), 1);
@@ -561,6 +585,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(bSdPfull, 1);
     mbar_init(bPdSfull, 256);
     mbar_init(bSdPfree, 256);
+    mbar_init(bPfree, 1);
+    mbar_init(bCSfull, 1);
     mbar_init(bdQfull, 1);
     mbar_init(bdQempty, 128);
     mbar_init(bAccFull, 1);
@@ -591,6 +617,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         mbar_expect_tx(bQdOfull(stage), 2 * kTileBytes);
         tma_load_2d(sQ + stage * kTileBytes, &tm_qkv, bQdOfull(stage), h * 64, row0 + i * 128);
         tma_load_2d(sdO + stage * kTileBytes, &tm_do, bQdOfull(stage), h * 64, row0 + i * 128);
+      }
+      if (n_it > 0) {
+        // one more turn of the ring: (cos, sin) of the 128 key rows, for the transposed rotation of dK at the end —
+        // fetched two tiles ahead of its use instead of from global memory when every SM's tail is waiting on L2
+        const int stage = n_it % 3;
+        mbar_wait(bStageEmpty(stage), ((n_it / 3) & 1) ^ 1u);
+        mbar_expect_tx(bCSfull, 2 * kTileBytes);
+        tma_load_2d(sQ + stage * kTileBytes, &tm_cs, bCSfull, 0, key0);     // pairs 0..15  (compute half 0)
+        tma_load_2d(sdO + stage * kTileBytes, &tm_cs, bCSfull, 32, key0);   // pairs 16..31 (compute half 1)
       }
     }
     __syncwarp();
@@ -654,6 +689,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + k * 2048, kTileBytes, 1024);
           umma_bf16_ss_p(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u, lead);
         }
+        tc_commit_p(bPfree, lead);  // P may be overwritten while dK and dQ are still being computed
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const uint64_t da = umma_smem_desc(sdSb + k * 2048, kTileBytes, 1024);
@@ -707,7 +743,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tma_store_commit();
       }
     }
+    TRACE(7, 0);
     if (r == 0) tma_store_wait<0>();
+    TRACE(7, 1);
   } else if (warp < 8) {
     // ============================== compute warps (256 threads: row r, column half `half`) ==============================
     reg_alloc<168>();
@@ -715,18 +753,34 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const int half = tid >> 7;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     constexpr float c2 = kSoftmaxScale * kLog2e;
+    // per-row statistics of a query tile; those of tile it + 1 are requested while tile it is being worked on, so
+    // their global-memory latency stays off the loop's critical path
+    float n_lse = 0.f, n_dlt = 0.f;
+    int n_ds = 0, n_dshi = 0;
+    auto load_stats = [&](int it) {
+      const int i = i_lo + it;
+      const int t = min(i * 128 + r, T - 1);
+      const long stat_idx = (static_cast<long>(b) * NH + h) * T + t;
+      n_lse = __ldg(lse + stat_idx);
+      n_dlt = __ldg(delta + stat_idx);
+      if (doc_start) {
+        n_ds = __ldg(doc_start + seq_row0 + t);
+        n_dshi = __ldg(doc_start + seq_row0 + min(i * 128 + 127, T - 1));
+      }
+    };
+    if (n_it > 0) load_stats(0);
     for (int it = 0; it < n_it; ++it) {
       const int i = i_lo + it;
       const int t = i * 128 + r;
-      const long stat_idx = (static_cast<long>(b) * NH + h) * T + min(t, T - 1);
-      const float lse2 = lse[stat_idx] * kLog2e;
-      const float dlt_s = delta[stat_idx] * kSoftmaxScale;
-      const int ds_t = doc_start ? doc_start[seq_row0 + min(t, T - 1)] : 0;
-      const int ds_hi_of_tile = doc_start ? doc_start[seq_row0 + min(i * 128 + 127, T - 1)] : 0;
+      const float lse2 = n_lse * kLog2e;
+      const float dlt_s = n_dlt * kSoftmaxScale;
+      const int ds_t = n_ds;
+      const int ds_hi_of_tile = n_dshi;
       const bool need_mask = (key0 + 127 > i * 128) || (key0 < ds_hi_of_tile);
       TRACE(half, it * 4 + 0);
       mbar_wait(bSdPfull, it & 1);
       tc_fence_after();
+      if (it + 1 < n_it) load_stats(it + 1);
       TRACE(half, it * 4 + 1);
       // the math for this thread's 64 columns stays in registers ...
       uint32_t pk_p[2][16], pk_ds[2][16];
@@ -743,9 +797,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
         if (need_mask) chunk_p_ds<true>(sr, pr, c2, lse2, dlt_s, ds_t - key0 - col0, t - key0 - col0, pk_p[c], pk_ds[c]);
         else chunk_p_ds<false>(sr, pr, c2, lse2, dlt_s, 0, 0, pk_p[c], pk_ds[c]);
+        // P leaves for shared memory chunk by chunk, under the math of the next chunk: its buffer is free as soon as
+        // the previous tile's dV MMAs are done (dS has to wait for dK and dQ as well)
+        if (c == 0 && it > 0) mbar_wait(bPfree, (it - 1) & 1);
+        {
+          const uint32_t rowoff = half * kTileBytes + r * 128;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
+            st_shared_v4(sP + off, make_uint4(pk_p[c][v * 4], pk_p[c][v * 4 + 1], pk_p[c][v * 4 + 2], pk_p[c][v * 4 + 3]));
+          }
+        }
       }
       // ... until the previous tile's dV/dK/dQ MMAs (which read P and dS from shared memory) have completed
+      TRACE(half, it * 4 + 2);
       if (it > 0) mbar_wait(bdQfull, (it - 1) & 1);
+      TRACE(half, it * 4 + 3);
       {
         const uint32_t rowoff = half * kTileBytes + r * 128;
 #pragma unroll
@@ -753,64 +820,88 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 #pragma unroll
           for (int v = 0; v < 4; ++v) {
             const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
-            st_shared_v4(sP + off, make_uint4(pk_p[c][v * 4], pk_p[c][v * 4 + 1], pk_p[c][v * 4 + 2], pk_p[c][v * 4 + 3]));
             st_shared_v4(sdS + off, make_uint4(pk_ds[c][v * 4], pk_ds[c][v * 4 + 1], pk_ds[c][v * 4 + 2], pk_ds[c][v * 4 + 3]));
           }
       }
+      TRACE(2 + half, it * 4 + 0);
       // dS a second time, into tensor memory (32 columns of bf16 pairs per thread), for dQ = dS.K
       tmem_st_32x32b_x16(tdS + lane_off + half * 32, pk_ds[0]);
       tmem_st_32x32b_x16(tdS + lane_off + half * 32 + 16, pk_ds[1]);
       tmem_st_wait();
+      TRACE(2 + half, it * 4 + 1);
       tc_fence_before();
       fence_proxy_async_smem();
+      TRACE(2 + half, it * 4 + 2);
       mbar_arrive(bPdSfull);
-      TRACE(half, it * 4 + 2);
-      TRACE(half, it * 4 + 3);
+      TRACE(2 + half, it * 4 + 3);
     }
     // ---- tail: dK / dV
+    TRACE(6, 0);
     if (n_it > 0) {
       mbar_wait(bAccFull, 0);
       tc_fence_after();
+      TRACE(6, 1);
       // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
       uint32_t kr[32], vr[32];
       tmem_ld_32x32b_x32(tdK + lane_off + half * 32, kr);
       tmem_ld_32x32b_x32(tdV + lane_off + half * 32, vr);
       tmem_ld_wait();
-      const int tk = key0 + r;
-      if (tk < T) {
-        __nv_bfloat16* krow = dqkv + (seq_row0 + tk) * ld + d + h * 64 + half * 32;
-        __nv_bfloat16* vrow = dqkv + (seq_row0 + tk) * ld + 2 * d + h * 64 + half * 32;
-        const float4* cs = reinterpret_cast<const float4*>(cos_sin + (static_cast<long>(tk) * 32 + half * 16) * 2);
+      TRACE(6, 6);
+      // (cos, sin) of this key row: in the ring slot after the last Q / dO tile, 128B-swizzled rows of 32 floats
+      mbar_wait(bCSfull, 0);
+      const uint32_t cs_row = (half == 0 ? sQ : sdO) + (n_it % 3) * kTileBytes + r * 128;
+      // dV and dK (un-rotated) leave as two 128 x 64 bf16 tiles through the P buffer and one TMA store each
+      const uint32_t out_row = sP + r * 128;
 #pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          uint4 o;
-          o.x = pack_bf16x2(__uint_as_float(vr[v * 8 + 0]), __uint_as_float(vr[v * 8 + 1]));
-          o.y = pack_bf16x2(__uint_as_float(vr[v * 8 + 2]), __uint_as_float(vr[v * 8 + 3]));
-          o.z = pack_bf16x2(__uint_as_float(vr[v * 8 + 4]), __uint_as_float(vr[v * 8 + 5]));
-          o.w = pack_bf16x2(__uint_as_float(vr[v * 8 + 6]), __uint_as_float(vr[v * 8 + 7]));
-          *reinterpret_cast<uint4*>(vrow + v * 8) = o;
-          // dK: transpose of the rotation, applied to the fp32 accumulators
-          const float4 c0 = __ldg(cs + 2 * v), c1 = __ldg(cs + 2 * v + 1);
-          const float g0 = __uint_as_float(kr[v * 8 + 0]), g1 = __uint_as_float(kr[v * 8 + 1]);
-          const float g2 = __uint_as_float(kr[v * 8 + 2]), g3 = __uint_as_float(kr[v * 8 + 3]);
-          const float g4 = __uint_as_float(kr[v * 8 + 4]), g5 = __uint_as_float(kr[v * 8 + 5]);
-          const float g6 = __uint_as_float(kr[v * 8 + 6]), g7 = __uint_as_float(kr[v * 8 + 7]);
-          uint4 q;
-          q.x = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
-          q.y = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
-          q.z = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
-          q.w = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
-          *reinterpret_cast<uint4*>(krow + v * 8) = q;
-        }
+      for (int v = 0; v < 4; ++v) {
+        uint4 o;
+        o.x = pack_bf16x2(__uint_as_float(vr[v * 8 + 0]), __uint_as_float(vr[v * 8 + 1]));
+        o.y = pack_bf16x2(__uint_as_float(vr[v * 8 + 2]), __uint_as_float(vr[v * 8 + 3]));
+        o.z = pack_bf16x2(__uint_as_float(vr[v * 8 + 4]), __uint_as_float(vr[v * 8 + 5]));
+        o.w = pack_bf16x2(__uint_as_float(vr[v * 8 + 6]), __uint_as_float(vr[v * 8 + 7]));
+        st_shared_v4(out_row + (((half * 4 + v) ^ (r & 7)) << 4), o);
+        // dK: transpose of the rotation, applied to the fp32 accumulators
+        const uint4 u0 = ld_shared_v4(cs_row + (((2 * v) ^ (r & 7)) << 4));
+        const uint4 u1 = ld_shared_v4(cs_row + (((2 * v + 1) ^ (r & 7)) << 4));
+        const float4 c0 = make_float4(__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w));
+        const float4 c1 = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w));
+        const float g0 = __uint_as_float(kr[v * 8 + 0]), g1 = __uint_as_float(kr[v * 8 + 1]);
+        const float g2 = __uint_as_float(kr[v * 8 + 2]), g3 = __uint_as_float(kr[v * 8 + 3]);
+        const float g4 = __uint_as_float(kr[v * 8 + 4]), g5 = __uint_as_float(kr[v * 8 + 5]);
+        const float g6 = __uint_as_float(kr[v * 8 + 6]), g7 = __uint_as_float(kr[v * 8 + 7]);
+        uint4 q;
+        q.x = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
+        q.y = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
+        q.z = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
+        q.w = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
+        st_shared_v4(out_row + kTileBytes + (((half * 4 + v) ^ (r & 7)) << 4), q);
       }
+      fence_proxy_async_smem();
+      named_bar_sync(2, 256);
+      if (tid == 0) {
+        const int row0 = static_cast<int>(seq_row0) + key0;
+        tma_store_2d(&tm_dqkv, sP, 2 * d + h * 64, row0);
+        tma_store_2d(&tm_dqkv, sP + kTileBytes, d + h * 64, row0);
+        tma_store_commit();
+        tma_store_wait_read<0>();  // shared memory is given up when the CTA exits
+      }
+      TRACE(6, 2);
     }
   }
   tc_fence_before();
   __syncthreads();
+  TRACE(6, 3);
   if (warp == 12) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
+#ifdef PCV_TRACE
+  TRACE(6, 4);
+  if (tid == 0 && cta_lin < 4096) {
+    g_cta_trace[cta_lin * 4 + 1] = gtimer();
+    g_cta_trace[cta_lin * 4 + 3] = n_it;
+  }
+#endif
 }
 
 // dqkv[:, q columns] = bf16( R(-theta) . dq_acc )    (dq_acc fp32 [B*T][d])
@@ -869,6 +960,9 @@ static int attn_check(int B, int T, int NH) {
 extern "C" int pcv_debug_read_trace(long long* host, int n) {
   return static_cast<int>(cudaMemcpyFromSymbol(host, pcv::g_trace, sizeof(long long) * n));
 }
+extern "C" int pcv_debug_read_cta_trace(long long* host, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host, pcv::g_cta_trace, sizeof(long long) * n));
+}
 #endif
 
 extern "C" int pcv_rope_qk(void* qkv, const float* cos_sin, int B, int T, int n_heads, void* stream) {
@@ -926,6 +1020,11 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   CUtensorMap tm_dq;
   rc = get_tmap_2d_f32(&tm_dq, dq_acc, BT, d, d, 128);
   if (rc) return rc;
+  CUtensorMap tm_cs, tm_dqkv;
+  rc = get_tmap_2d_f32(&tm_cs, cos_sin, T, 64, 64, 128);  // rows = positions, 32 x (cos, sin); boxes of 32 floats
+  if (rc) return rc;
+  rc = get_tmap_2d_bf16(&tm_dqkv, dqkv, BT, 3 * d, 3 * d, 128);
+  if (rc) return rc;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnBwdSmem::kBytes);
@@ -941,7 +1040,7 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   }
   dim3 grid(T / 128, n_heads, B);
   attn_bwd_kernel<<<grid, kAttnBwdThreads, AttnBwdSmem::kBytes, st>>>(
-      tm_qkv, tm_do, tm_dq, cos_sin, doc_start, lse, delta, dq_acc,
+      tm_qkv, tm_do, tm_dq, tm_cs, tm_dqkv, cos_sin, doc_start, lse, delta, dq_acc,
       static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
   {
     const long total = BT * (d / 8);

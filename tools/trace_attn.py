@@ -45,14 +45,46 @@ lib.pcv_debug_read_trace(buf, 8192)
 a = np.array(buf[:], dtype=np.int64).reshape(8, 1024)
 t0 = a[0, 0]
 for hf in range(2):
-    print(f"--- bwd compute half{hf} (key tile 0: 16 q tiles): [wait_SdP, dQ-readout+red, compute+arrive, loop] @abs")
+    print(f"--- bwd compute half{hf} (key tile 0: 16 q tiles): [wait_SdP, ld+math, wait dQfull(it-1), store P/dS+arrive] @abs")
     s = a[hf]
     for i in range(16):
         x = s[i * 4:i * 4 + 5]
         print(i, x[1] - x[0], x[2] - x[1], x[3] - x[2], (x[4] - x[3]) if i < 15 else -1, " @", x[0] - t0)
+print("--- bwd compute half0 store phase: [sts issue, tmem_st+wait, fences, arrive, to next tile start]")
+for i in range(15):
+    x = a[2][i * 4:i * 4 + 4]
+    print(i, int(x[0] - a[0][i * 4 + 3]), int(x[1] - x[0]), int(x[2] - x[1]), int(x[3] - x[2]), int(a[0][(i + 1) * 4] - x[3]))
 m = a[4]
-print("--- bwd MMA: (wait for PdS, then until next wait) ")
-print([(int(m[i * 2 + 1] - m[i * 2]), int(m[i * 2 + 2] - m[i * 2 + 1]) if i < 15 else -1) for i in range(16)])
 m5 = a[5]
-print("--- bwd MMA detail per tile: [PdS->QdO ready, issue SdP, wait dQempty, issue dV/dK/dQ + commits]")
-print([(int(m5[i * 4] - m[i * 2 + 1]), int(m5[i * 4 + 1] - m5[i * 4]), int(m5[i * 4 + 2] - m5[i * 4 + 1]), int(m5[i * 4 + 3] - m5[i * 4 + 2])) for i in range(15)])
+print("--- bwd MMA per tile: [wait QdO+SdPfree, issue SdP(it+1), wait PdSfull(it), wait dQempty, issue dV/dK/dQ] @abs")
+for i in range(16):
+    print(i, int(m5[i * 4] - m[i * 2]), int(m5[i * 4 + 1] - m5[i * 4]), int(m[i * 2 + 1] - m5[i * 4 + 1]) if i < 15 else int(m[i*2+1]-m[i*2]),
+          int(m5[i * 4 + 2] - m[i * 2 + 1]), int(m5[i * 4 + 3] - m5[i * 4 + 2]), " @", int(m[i * 2] - t0))
+
+e = a[6]
+print("--- bwd CTA(0,0,0) ends (cycles from CTA start): first S/dP ready", int(a[0][1] - e[5]), " loop done", int(e[0] - e[5]),
+      " cs loaded", int(e[7] - e[5]), " dK/dV accumulated", int(e[1] - e[5]), " in registers", int(e[6] - e[5]), " dK/dV written", int(e[2] - e[5]), " all warps done", int(e[3] - e[5]),
+      " TMEM freed", int(e[4] - e[5]), " | dQ warpgroup: loop done", int(a[7][0] - e[5]), " reduce-adds complete", int(a[7][1] - e[5]))
+# ---- backward: occupancy of the SMs by CTAs (globaltimer at CTA entry / exit)
+cbuf = (ctypes.c_longlong * (4096 * 4))()
+lib.pcv_debug_read_cta_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
+lib.pcv_debug_read_cta_trace(cbuf, 4096 * 4)
+c = np.array(cbuf[:], dtype=np.int64).reshape(4096, 4)[:B * NH * (T // 128)]
+t_begin, t_end = c[:, 0].min(), c[:, 1].max()
+print(f"--- bwd CTA occupancy: kernel span {(t_end - t_begin) / 1e3:.1f} us, {len(c)} CTAs on {len(set(c[:, 2]))} SMs")
+busy = (c[:, 1] - c[:, 0]).sum() / 1e3
+print(f"sum of CTA lifetimes {busy:.0f} us = {busy / 148:.1f} us per SM; per-iteration-count mean lifetime (us):")
+for n in sorted(set(c[:, 3])):
+    sel = c[c[:, 3] == n]
+    print(f"  n_it={n:2d}: {((sel[:, 1] - sel[:, 0]).mean()) / 1e3:7.2f}", end="")
+print()
+gaps, last_end = [], []
+for sm in sorted(set(c[:, 2])):
+    sel = c[c[:, 2] == sm]
+    sel = sel[np.argsort(sel[:, 0])]
+    gaps += list((sel[1:, 0] - sel[:-1, 1]) / 1e3)
+    last_end.append((sel[-1, 1] - t_begin) / 1e3)
+gaps = np.array(gaps)
+print(f"gap between consecutive CTAs on an SM: mean {gaps.mean():.2f} us, median {np.median(gaps):.2f}, max {gaps.max():.2f}, total per SM {gaps.sum() / 148:.1f} us")
+le = np.array(last_end)
+print(f"SM finish times: min {le.min():.1f} median {np.median(le):.1f} max {le.max():.1f} us")
