@@ -181,7 +181,7 @@ __device__ __forceinline__ void chunk_softmax(const uint32_t* sr, float c2, floa
 //   warp 9          : tcgen05.mma issuer: S_w = Q_w.K_j^T, O_w += P_w.V_j, ping-ponged between the warpgroups
 // TMEM: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512) (bf16 pairs).
 __global__ void __launch_bounds__(kAttnThreads, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __restrict__ doc_start,
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_out, const int32_t* __restrict__ doc_start,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ lse, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -201,10 +201,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef PCV_TRACE
   const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 288);
+  const int cta_lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (tid == 0 && cta_lin < 4096) {
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_cta_trace[cta_lin * 4 + 0] = gtimer();
+    g_cta_trace[cta_lin * 4 + 2] = smid;
+  }
 #endif
-  const int n_qblk = gridDim.x;
-  const int qblk = n_qblk - 1 - blockIdx.x;  // heaviest (latest) query blocks first
-  const int h = blockIdx.y, b = blockIdx.z;
+  // launch order = blockIdx.x fastest, z slowest: every (head, batch) pair of the heaviest (latest) query block first,
+  // the lightest blocks last, so that the SMs run dry within one short CTA of each other
+  const int n_qblk = gridDim.z;
+  const int qblk = n_qblk - 1 - blockIdx.z;
+  const int h = blockIdx.x, b = blockIdx.y;
   const int d = NH * 64;
   const int q0 = qblk * 256;
   const long seq_row0 = static_cast<long>(b) * T;
@@ -226,8 +235,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
   const int jhi = jmax[1] >= 0 ? jmax[1] : jmax[0];
   auto active = [&](int w, int j) { return j >= jmin[w] && j <= jmax[w]; };
 
-  if (warp == 9 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_out);
     mbar_init(bQ, 1);
     for (int s = 0; s < 3; ++s) {
       mbar_init(bKfull(s), 1);
@@ -241,8 +251,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
       mbar_init(bPVdone(w), 1);
     }
     fence_mbar_init();
+    // Q and the first K / V tile are requested right away: their latency runs under the tensor-memory allocation and
+    // the block-wide barrier below
+    const int row0 = static_cast<int>(seq_row0);
+    const int nq = jmax[1] >= 0 ? 2 : 1;
+    mbar_expect_tx(bQ, nq * kTileBytes);
+    for (int w = 0; w < nq; ++w) tma_load_2d(sQ + w * kTileBytes, &tm_qkv, bQ, h * 64, row0 + q0 + 128 * w);
+    mbar_expect_tx(bKfull(0), kTileBytes);
+    tma_load_2d(sK, &tm_qkv, bKfull(0), d + h * 64, row0 + jlo * 128);
+    mbar_expect_tx(bVfull(0), kTileBytes);
+    tma_load_2d(sV, &tm_qkv, bVfull(0), 2 * d + h * 64, row0 + jlo * 128);
   }
-  if (warp == 8) tmem_alloc<512>(tmem_ptr_smem);
+  if (warp == 8) {
+    __syncwarp();
+    tmem_alloc<512>(tmem_ptr_smem);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -252,11 +275,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
     // ============================== TMA producer ==============================
     if (lane == 0) {
       const int row0 = static_cast<int>(seq_row0);
-      const int nq = jmax[1] >= 0 ? 2 : 1;
-      mbar_expect_tx(bQ, nq * kTileBytes);
-      for (int w = 0; w < nq; ++w) tma_load_2d(sQ + w * kTileBytes, &tm_qkv, bQ, h * 64, row0 + q0 + 128 * w);
-      int idx = 0;
-      for (int j = jlo; j <= jhi; ++j, ++idx) {
+      int idx = 1;
+      for (int j = jlo + 1; j <= jhi; ++j, ++idx) {
         const int slot = idx % 3;
         const uint32_t par = (idx / 3) & 1;
         TRACE(6, idx * 3 + 0);
@@ -433,8 +453,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
         tmem_ld_32x32b_x32(tO, o0);
         tmem_ld_32x32b_x32(tO + 32, o1);
         tmem_ld_wait();
-        if (t < T) {
-          __nv_bfloat16* orow = out + (seq_row0 + t) * d + h * 64;
+        // the 128 x 64 output tile leaves through this warpgroup's Q tile (all its S MMAs are long done) and one TMA
+        // store: whole 128-byte rows, nothing for the CTA's last instructions to wait on but the read of the tile
+        {
+          const uint32_t orow = sQ + w * kTileBytes + r * 128;
 #pragma unroll
           for (int v = 0; v < 4; ++v) {
             uint4 o;
@@ -442,7 +464,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
             o.y = pack_bf16x2(__uint_as_float(o0[v * 8 + 2]) * inv_l, __uint_as_float(o0[v * 8 + 3]) * inv_l);
             o.z = pack_bf16x2(__uint_as_float(o0[v * 8 + 4]) * inv_l, __uint_as_float(o0[v * 8 + 5]) * inv_l);
             o.w = pack_bf16x2(__uint_as_float(o0[v * 8 + 6]) * inv_l, __uint_as_float(o0[v * 8 + 7]) * inv_l);
-            *reinterpret_cast<uint4*>(orow + v * 8) = o;
+            st_shared_v4(orow + ((v ^ (r & 7)) << 4), o);
           }
 #pragma unroll
           for (int v = 0; v < 4; ++v) {
@@ -451,9 +473,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
             o.y = pack_bf16x2(__uint_as_float(o1[v * 8 + 2]) * inv_l, __uint_as_float(o1[v * 8 + 3]) * inv_l);
             o.z = pack_bf16x2(__uint_as_float(o1[v * 8 + 4]) * inv_l, __uint_as_float(o1[v * 8 + 5]) * inv_l);
             o.w = pack_bf16x2(__uint_as_float(o1[v * 8 + 6]) * inv_l, __uint_as_float(o1[v * 8 + 7]) * inv_l);
-            *reinterpret_cast<uint4*>(orow + 32 + v * 8) = o;
+            st_shared_v4(orow + (((4 + v) ^ (r & 7)) << 4), o);
           }
-          lse[(static_cast<long>(b) * NH + h) * T + t] = ref * kSoftmaxScale + logf(l_run);
+          fence_proxy_async_smem();
+          named_bar_sync(1 + w, 128);
+          if (r == 0) {
+            tma_store_2d(&tm_out, sQ + w * kTileBytes, h * 64, static_cast<int>(seq_row0) + q0 + 128 * w);
+            tma_store_commit();
+          }
+          if (t < T) lse[(static_cast<long>(b) * NH + h) * T + t] = ref * kSoftmaxScale + logf(l_run);
+          if (r == 0) tma_store_wait_read<0>();  // shared memory is given up when the CTA exits
         }
       }
     }
@@ -464,6 +493,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const int32_t* __res
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
+#ifdef PCV_TRACE
+  if (tid == 0 && cta_lin < 4096) {
+    g_cta_trace[cta_lin * 4 + 1] = gtimer();
+    g_cta_trace[cta_lin * 4 + 3] = jhi - jlo + 1;
+  }
+#endif
 }
 
 // ================================================================================================ backward
@@ -550,9 +585,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
 #endif
   TRACE(6, 5);
-  const int j = blockIdx.x;  // key tile
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int d = NH * 64, ld = 3 * d;
+  // launch order (x fastest, z slowest): per sequence, key tile 0 of every head first (all query tiles visible: the
+  // longest loop), the one-tile loops last.  Sequences stay apart so that the fp32 dQ accumulator lines the reduce-adds
+  // hit (8 MB per sequence) stay in L2 instead of cycling through it.
+  const int j = blockIdx.y;
+  const int h = blockIdx.x, b = blockIdx.z;
+  const int d = NH * 64;
   const long seq_row0 = static_cast<long>(b) * T;
   const int n_qt = (T + 127) / 128;
   const int key0 = j * 128;
@@ -571,7 +609,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
   const int n_it = i_hi - i_lo + 1;
 
-  if (warp == 13 && lane == 0) {
+  if (warp == 12 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     tma_prefetch_desc(&tm_dq);
@@ -591,8 +629,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(bdQempty, 128);
     mbar_init(bAccFull, 1);
     fence_mbar_init();
+    // K, V and the first Q / dO tile are requested right away: their latency runs under the tensor-memory allocation
+    // and the block-wide barrier below
+    const int row0 = static_cast<int>(seq_row0);
+    mbar_expect_tx(bKVfull, 2 * kTileBytes);
+    tma_load_2d(sK, &tm_qkv, bKVfull, d + h * 64, row0 + key0);
+    tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + h * 64, row0 + key0);
+    if (n_it > 0) {
+      mbar_expect_tx(bQdOfull(0), 2 * kTileBytes);
+      tma_load_2d(sQ, &tm_qkv, bQdOfull(0), h * 64, row0 + i_lo * 128);
+      tma_load_2d(sdO, &tm_do, bQdOfull(0), h * 64, row0 + i_lo * 128);
+    }
   }
-  if (warp == 12) tmem_alloc<512>(tmem_ptr_smem);
+  if (warp == 12) {
+    __syncwarp();
+    tmem_alloc<512>(tmem_ptr_smem);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -607,10 +659,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     // ============================== TMA producer (q, k in qkv are already rotated) ==============================
     if (lane == 0) {
       const int row0 = static_cast<int>(seq_row0);
-      mbar_expect_tx(bKVfull, 2 * kTileBytes);
-      tma_load_2d(sK, &tm_qkv, bKVfull, d + h * 64, row0 + key0);
-      tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + h * 64, row0 + key0);
-      for (int it = 0; it < n_it; ++it) {
+      for (int it = 1; it < n_it; ++it) {
         const int i = i_lo + it;
         const int stage = it % 3;
         mbar_wait(bStageEmpty(stage), ((it / 3) & 1) ^ 1u);
@@ -990,15 +1039,18 @@ extern "C" int pcv_attn_fwd(const void* qkv, const int32_t* doc_start, void* out
   CUtensorMap tm;
   rc = get_tmap_2d_bf16(&tm, qkv, static_cast<uint64_t>(B) * T, 3 * d, 3 * d, 128);
   if (rc) return rc;
+  CUtensorMap tm_out;
+  rc = get_tmap_2d_bf16(&tm_out, out, static_cast<uint64_t>(B) * T, d, d, 128);
+  if (rc) return rc;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnFwdSmem::kBytes);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr = true;
   }
-  dim3 grid((T + 255) / 256, n_heads, B);
+  dim3 grid(n_heads, B, (T + 255) / 256);
   attn_fwd_kernel<<<grid, kAttnThreads, AttnFwdSmem::kBytes, static_cast<cudaStream_t>(stream)>>>(
-      tm, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
+      tm, tm_out, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
   count_launch();
   return cuda_rc();
 }
@@ -1038,7 +1090,7 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
     attn_bwd_prep_kernel<<<static_cast<int>((threads + 255) / 256), 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, static_cast<int>(BT), T, n_heads);
   }
-  dim3 grid(T / 128, n_heads, B);
+  dim3 grid(n_heads, T / 128, B);
   attn_bwd_kernel<<<grid, kAttnBwdThreads, AttnBwdSmem::kBytes, st>>>(
       tm_qkv, tm_do, tm_dq, tm_cs, tm_dqkv, cos_sin, doc_start, lse, delta, dq_acc,
       static_cast<__nv_bfloat16*>(dqkv), T, n_heads);

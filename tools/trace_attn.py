@@ -15,6 +15,31 @@ for _ in range(3):
     out, lse = ops.attn_fwd(qkv, None, B, T, NH)
 torch.cuda.synchronize()
 lib = _lib.load()
+
+def cta_report(tag, n_cta):
+    cbuf = (ctypes.c_longlong * (4096 * 4))()
+    lib.pcv_debug_read_cta_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    lib.pcv_debug_read_cta_trace(cbuf, 4096 * 4)
+    c = np.array(cbuf[:], dtype=np.int64).reshape(4096, 4)[:n_cta]
+    t_begin, t_end = c[:, 0].min(), c[:, 1].max()
+    print(f"--- {tag} CTA occupancy: kernel span {(t_end - t_begin) / 1e3:.1f} us, {len(c)} CTAs on {len(set(c[:, 2]))} SMs")
+    busy = (c[:, 1] - c[:, 0]).sum() / 1e3
+    print(f"sum of CTA lifetimes {busy:.0f} us = {busy / 148:.1f} us per SM; mean lifetime (us) by number of key/query tiles visited:")
+    for n in sorted(set(c[:, 3])):
+        sel = c[c[:, 3] == n]
+        print(f"  n={n:2d}: {((sel[:, 1] - sel[:, 0]).mean()) / 1e3:7.2f}", end="")
+    print()
+    gaps, last_end = [], []
+    for sm in sorted(set(c[:, 2])):
+        sel = c[c[:, 2] == sm]
+        sel = sel[np.argsort(sel[:, 0])]
+        gaps += list((sel[1:, 0] - sel[:-1, 1]) / 1e3)
+        last_end.append((sel[-1, 1] - t_begin) / 1e3)
+    gaps = np.array(gaps)
+    print(f"gap between consecutive CTAs on an SM: mean {gaps.mean():.2f} us, median {np.median(gaps):.2f}, max {gaps.max():.2f}, total per SM {gaps.sum() / 148:.1f} us")
+    le = np.array(last_end)
+    print(f"SM finish times: min {le.min():.1f} median {np.median(le):.1f} max {le.max():.1f} us")
+
 buf = (ctypes.c_longlong * 8192)()
 lib.pcv_debug_read_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
 print("rc", lib.pcv_debug_read_trace(buf, 8192))
@@ -35,6 +60,8 @@ for w in range(2):
 ld = a[6]
 print("--- fwd loader (thread 256): per K tile [wait empty slot, load+rope+store] @abs")
 print([(int(ld[i * 3 + 1] - ld[i * 3]), int(ld[i * 3 + 2] - ld[i * 3 + 1]), int(ld[i * 3] - t0)) for i in range(16)])
+
+cta_report('fwd', B * NH * ((T + 255) // 256))
 
 # ---- backward
 dout = torch.randn(B * T, d, device="cuda").to(torch.bfloat16)
@@ -65,26 +92,4 @@ e = a[6]
 print("--- bwd CTA(0,0,0) ends (cycles from CTA start): first S/dP ready", int(a[0][1] - e[5]), " loop done", int(e[0] - e[5]),
       " cs loaded", int(e[7] - e[5]), " dK/dV accumulated", int(e[1] - e[5]), " in registers", int(e[6] - e[5]), " dK/dV written", int(e[2] - e[5]), " all warps done", int(e[3] - e[5]),
       " TMEM freed", int(e[4] - e[5]), " | dQ warpgroup: loop done", int(a[7][0] - e[5]), " reduce-adds complete", int(a[7][1] - e[5]))
-# ---- backward: occupancy of the SMs by CTAs (globaltimer at CTA entry / exit)
-cbuf = (ctypes.c_longlong * (4096 * 4))()
-lib.pcv_debug_read_cta_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
-lib.pcv_debug_read_cta_trace(cbuf, 4096 * 4)
-c = np.array(cbuf[:], dtype=np.int64).reshape(4096, 4)[:B * NH * (T // 128)]
-t_begin, t_end = c[:, 0].min(), c[:, 1].max()
-print(f"--- bwd CTA occupancy: kernel span {(t_end - t_begin) / 1e3:.1f} us, {len(c)} CTAs on {len(set(c[:, 2]))} SMs")
-busy = (c[:, 1] - c[:, 0]).sum() / 1e3
-print(f"sum of CTA lifetimes {busy:.0f} us = {busy / 148:.1f} us per SM; per-iteration-count mean lifetime (us):")
-for n in sorted(set(c[:, 3])):
-    sel = c[c[:, 3] == n]
-    print(f"  n_it={n:2d}: {((sel[:, 1] - sel[:, 0]).mean()) / 1e3:7.2f}", end="")
-print()
-gaps, last_end = [], []
-for sm in sorted(set(c[:, 2])):
-    sel = c[c[:, 2] == sm]
-    sel = sel[np.argsort(sel[:, 0])]
-    gaps += list((sel[1:, 0] - sel[:-1, 1]) / 1e3)
-    last_end.append((sel[-1, 1] - t_begin) / 1e3)
-gaps = np.array(gaps)
-print(f"gap between consecutive CTAs on an SM: mean {gaps.mean():.2f} us, median {np.median(gaps):.2f}, max {gaps.max():.2f}, total per SM {gaps.sum() / 148:.1f} us")
-le = np.array(last_end)
-print(f"SM finish times: min {le.min():.1f} median {np.median(le):.1f} max {le.max():.1f} us")
+cta_report('bwd', B * NH * (T // 128))
