@@ -432,20 +432,21 @@ struct PairCfgT {
   static constexpr int kTileM = 256;
   // the fused epilogues trade one pipeline stage for a second 4 KB box per epilogue warp (two stores in flight, or the
   // saved gate and up slabs of the SwiGLU backward brought in by TMA while the previous slab is still being worked on)
-  static constexpr int kStages = kFused ? 5 : 6;
+  static constexpr int kStages = EPI == EPI_DSWIGLU ? 4 : (kFused ? 5 : 6);
   static constexpr int kABytes = 128 * kBK * 2;  // this CTA's 128 rows of A
   static constexpr int kBBytes = 128 * kBK * 2;  // this CTA's 128 of the 256 B rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarBytes = 256;
   static constexpr int kEpiWarps = 8;
   static constexpr int kEpiBoxBytes = 32 * 128;  // 32 rows x 128 B (one 128B-swizzled TMA box)
-  static constexpr int kEpiBoxes = kFused ? 2 : 1;
+  static constexpr int kEpiBoxes = EPI == EPI_DSWIGLU ? 3 : (kFused ? 2 : 1);
   static constexpr int kEpiBufBytes = kEpiBoxes * kEpiBoxBytes;  // per epilogue warp
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + kBarBytes + 1024;
   static constexpr uint32_t kTmemCols = 512;  // two 256-column accumulators
 };
 using PairCfg = PairCfgT<0>;
-static_assert(PairCfgT<0>::kSmemBytes <= 232448 && PairCfgT<EPI_SWIGLU>::kSmemBytes <= 232448,
+static_assert(PairCfgT<0>::kSmemBytes <= 232448 && PairCfgT<EPI_SWIGLU>::kSmemBytes <= 232448 &&
+                  PairCfgT<EPI_DSWIGLU>::kSmemBytes <= 232448,
               "CTA-pair GEMM shared memory exceeds 227 KB");
 
 template <bool A_MN, bool B_MN, int EPI>
@@ -625,8 +626,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       // The saved gate and up values of a slab arrive by TMA in the warp's two boxes (requested as soon as the previous
       // slab's stores have read the boxes, i.e. while the MMAs of this tile still run), every lane reads its own row,
       // turns (dh, g, u) into (dg, du) in place and the two boxes leave again by TMA store.
-      const uint32_t box_g = buf, box_u = buf + Cfg::kEpiBoxBytes;
-      const uint32_t row_g = box_g + lane * 128, row_u = box_u + lane * 128;
+      const uint32_t box_g = buf, box_u = buf + Cfg::kEpiBoxBytes, box_o = buf + 2 * Cfg::kEpiBoxBytes;
+      const uint32_t row_g = box_g + lane * 128, row_u = box_u + lane * 128, row_o = box_o + lane * 128;
       const uint32_t ld_bar = bar_base + 8u * (2 * Cfg::kStages + 5 + (warp - 4));
       uint32_t ld_phase = 0;
       // slab (w, sl) of this warp: first column / first row, and whether any of it lies inside the matrix
@@ -685,6 +686,13 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             pg[v] = ld_shared_v4(row_g + ((v ^ sw) << 4));
             pu[v] = ld_shared_v4(row_u + ((v ^ sw) << 4));
           }
+          __syncwarp();
+          // both input boxes are in registers: the slab after this one can be on its way during the math
+          nw = w;
+          nsl = sl;
+          if (nsl == 0) nsl = 1;
+          else { nsl = 0; nw += npairs; }
+          if (seek(nw, nsl, nc, nr) && lane == 0) request(nc, nr);
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             uint32_t r[32];
@@ -698,32 +706,21 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
               dswiglu32(r, p.alpha, pg + 4 * half, pu + 4 * half);
             }
           }
-#pragma unroll
-          for (int v = 0; v < 8; ++v) {
-            st_shared_v4(row_g + ((v ^ sw) << 4), pg[v]);
-            st_shared_v4(row_u + ((v ^ sw) << 4), pu[v]);
-          }
-          fence_proxy_async_smem();
-          __syncwarp();
           if (prof) { const unsigned int t = clk32(); pf2 += t - pt; pt = t; }
-          // the slab after this one
-          nw = w;
-          nsl = sl;
-          if (nsl == 0) nsl = 1;
-          else { nsl = 0; nw += npairs; }
-          const bool more = seek(nw, nsl, nc, nr);
-          if (lane == 0) {
-            if (!(p.dbg & 1)) {
-              tma_store_2d(&tma_c, box_g, sl == 0 ? c0 : c1, row0);
-              tma_store_2d(&tma_c2, box_u, sl == 0 ? c0 : c1, row0);
+          // dg, then du, through the third box
+#pragma unroll
+          for (int o = 0; o < 2; ++o) {
+            if (lane == 0) tma_store_wait_read<0>();  // the previous store has read the box
+            __syncwarp();
+#pragma unroll
+            for (int v = 0; v < 8; ++v) st_shared_v4(row_o + ((v ^ sw) << 4), o == 0 ? pg[v] : pu[v]);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && !(p.dbg & 1)) {
+              tma_store_2d(o == 0 ? &tma_c : &tma_c2, box_o, sl == 0 ? c0 : c1, row0);
               tma_store_commit();
             }
-            if (more) {
-              tma_store_wait_read<0>();  // both boxes have been read by the stores: they can take the next slab
-              request(nc, nr);
-            }
           }
-          __syncwarp();
           if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
         }
       }

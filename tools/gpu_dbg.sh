@@ -1,5 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_kernels_gpu.py -m gpu -x -q -k "attention" 2>&1 | tail -3
-timeout 300 python tools/bench_kernels.py 2048 attn 2>&1 | tail -4
-python tools/trace_attn.py 2>&1 | grep -A52 "bwd compute half0 (key"
+timeout 600 python -m pytest tests/test_kernels_gpu.py -m gpu -x -q -k "swiglu or linear" 2>&1 | tail -2
+PCV_KB_CUBLAS=0 timeout 120 python tools/bench_kernels.py 2048 fused 2>&1 | grep "#1"
+timeout 300 python tools/prof_epilogue.py 2>&1 | tail -4
