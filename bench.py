@@ -69,6 +69,16 @@ def gemm_flops_per_token(c: dict) -> float:
     return 6.0 * (L * (4 * d * d + 3 * d * hid) + d * V)
 
 
+def load_gemm_traffic(cname: str):
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one step's GEMM launches, from the committed
+    `ncu --set full` capture summarised by tools/gemm_traffic.py (C3 shapes only); None when there is no capture."""
+    p = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
+    if cname != "c3" or not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f).get("step_bytes")
+
+
 def load_peaks() -> dict:
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -348,7 +358,11 @@ def gpu_main(args) -> None:
             "gpu_launches": int(launches), "clocks": clocks, "loss": loss_val,
             "roofline": {"kernel": "pcv::gemm_bf16_kernel (all Dense fwd/dgrad/wgrad launches of one step)",
                          "bound": "tensor", "achieved": gemm_tf, "peak": peaks["bf16_tflops_sustained"] / 1.0,
-                         "unit": "TFLOP/s", "frac": gemm_tf / peaks["bf16_tflops_sustained"], "traffic": None,
+                         "unit": "TFLOP/s", "frac": gemm_tf / peaks["bf16_tflops_sustained"],
+                         "traffic": load_gemm_traffic(args.config),
+                         "traffic_note": "DRAM bytes of the same launches (one step), ncu --set full, "
+                                         "profiles/r01_gemm_traffic.json; algorithmic flops per step = "
+                                         f"{gemm_flops_per_token(c) * B * T:.4g}",
                          "peak_source": peaks["_source"] + " bf16_tflops_sustained",
                          "gemm_ms_per_step": gemm_ms, "gemm_share_of_step": gemm_ms / ms_step},
         }

@@ -103,6 +103,47 @@ if which == "fused":
         ms = timeit(lambda: ops.swiglu_bwd(gu_s, dh))
         res[f"swiglu_bwd#{rep}"] = (ms, 5 * M * hp * 2 / ms / 1e6, "GB/s")
 
+if which == "gemmstep":
+    # every GEMM launch of one transformer block (forward, then backward) and of the LM head, once each, in the order a
+    # training step issues them: the input of tools/gemm_traffic.py (DRAM bytes per launch from `ncu --set full`)
+    xd = torch.randn(M, d, device=dev).to(bf)
+    xh = torch.randn(M, hp, device=dev).to(bf)
+    y3 = torch.randn(M, 3 * d, device=dev).to(bf)
+    y2h = torch.randn(M, 2 * hp, device=dev).to(bf)
+    wq = (torch.randn(d, 3 * d, device=dev) * 0.02).to(bf)
+    wo = (torch.randn(d, d, device=dev) * 0.02).to(bf)
+    wgu = (torch.randn(d, 2 * hp, device=dev) * 0.02).to(bf)
+    wdn = (torch.randn(hp, d, device=dev) * 0.02).to(bf)
+    wlm = (torch.randn(d, Vp, device=dev) * 0.02).to(bf)
+    cs_t = ops.rope_table(64, T, 500000.0, dev)
+    gq, go, ggu, gdn, glm = (torch.zeros_like(w, dtype=torch.float32) for w in (wq, wo, wgu, wdn, wlm))
+
+    def layer_and_head():
+        ops.linear_fwd_rope(xd, wq, cs_t, T, 2 * d)
+        ops.linear_fwd(xd, wo)
+        gu_s, _ = ops.linear_fwd_swiglu(xd, wgu)
+        ops.linear_fwd(xh, wdn)
+        ops.linear_dgrad_dswiglu(xd, wdn, gu_s)
+        ops.linear_wgrad(xh, xd, gdn)
+        ops.linear_dgrad(y2h, wgu)
+        ops.linear_wgrad(xd, y2h, ggu)
+        ops.linear_dgrad(xd, wo)
+        ops.linear_wgrad(xd, xd, go)
+        ops.linear_dgrad(y3, wq)
+        ops.linear_wgrad(xd, y3, gq)
+        logits = ops.linear_fwd(xd, wlm)
+        ops.linear_dgrad(logits, wlm)
+        ops.linear_wgrad(xd, logits, glm)
+
+    for _ in range(int(os.environ.get("PCV_KB_WARM", 1))):
+        layer_and_head()
+    torch.cuda.synchronize()
+    flush.zero_()
+    torch.cuda.synchronize()
+    layer_and_head()
+    torch.cuda.synchronize()
+    print("gemmstep: 12 block GEMMs + 3 LM-head GEMMs launched")
+
 if which in ("all", "gemm"):
     def gemm_set(name, K, N):
         xx = torch.randn(M, K, device=dev).to(bf)

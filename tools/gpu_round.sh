@@ -16,5 +16,11 @@ PCV_KB_ITERS=1 PCV_KB_WARM=1 ncu --set full --clock-control none --import-source
 ncu -i gpurun_out/kernels_full.ncu-rep --page raw --csv > gpurun_out/kernels_full_raw.csv 2> /dev/null
 ncu -i gpurun_out/kernels_full.ncu-rep --page details --csv > gpurun_out/kernels_full_details.csv 2> /dev/null
 ls -la gpurun_out/kernels_full.ncu-rep; rm -f gpurun_out/kernels_full.ncu-rep
+# DRAM traffic of one step's GEMM launches (roofline.traffic): every GEMM of a block and of the LM head once
+PCV_KB_WARM=1 python tools/bench_kernels.py 2048 gemmstep > gpurun_out/plain3.log 2>&1 && \
+PCV_KB_WARM=1 ncu --set full --clock-control none -k regex:'gemm_bf16' -f -o gpurun_out/gemmstep \
+    python tools/bench_kernels.py 2048 gemmstep > gpurun_out/ncu_gemmstep.log 2>&1; echo "ncu3=$?"
+ncu -i gpurun_out/gemmstep.ncu-rep --page raw --csv > gpurun_out/gemmstep_raw.csv 2> /dev/null
+rm -f gpurun_out/gemmstep.ncu-rep
 fi
 tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench_c3.json
