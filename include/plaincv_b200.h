@@ -121,6 +121,20 @@ int pcv_mean2(const float* row_loss, const float* row_correct, float* out, int M
 /* out[i] += in[i] (bf16), helper for gradient joins of the residual stream */
 int pcv_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
 
+/* ---- the step after the hot path: global-norm clip + AdamW over flat fp32 buffers ----
+ * partials[b] = sum of g[i]^2 over block b's share (n_partials blocks, fixed order: reproducible norm).
+ * Replaces optax.global_norm in _clip_grads, train_lm.py:173-178. */
+int pcv_sumsq_partials(const float* g, long long n, float* partials, int n_partials, void* stream);
+/* One pass over n parameters: g *= min(1, max_norm / (sqrt(sum partials) + 1e-6)) (skipped when max_norm <= 0);
+ * m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr (m/(1-b1^step) / (sqrt(v/(1-b2^step)) + eps) + weight_decay p);
+ * p_bf16 (optional) = bf16(p), the compute copy.  step is 1-based.  Hyper-parameters are doubles so that 1 - b2 and
+ * the bias corrections are formed before rounding to fp32 (the arithmetic on the data is fp32, as in the reference).  norm_out (optional, device) receives the norm.
+ * Replaces _clip_grads + apply_grads (train_lm.py:173-178, 316-353) with optax.adamw (optim/factory.py:193-205)
+ * and flax's per-call promote_dtype of the parameters. */
+int pcv_adamw_step(float* p, const float* g, float* m, float* v, void* p_bf16, long long n, const float* partials,
+                   int n_partials, float* norm_out, double max_norm, double lr, double b1, double b2, double eps,
+                   double weight_decay, int step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

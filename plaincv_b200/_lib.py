@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_float, c_int, c_longlong, c_void_p
+from ctypes import c_double, c_float, c_int, c_longlong, c_void_p
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -55,6 +55,9 @@ SIGNATURES = {
                                c_void_p]),
     "pcv_mean2": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "pcv_add_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_longlong, c_void_p]),
+    "pcv_sumsq_partials": (c_int, [c_void_p, c_longlong, c_void_p, c_int, c_void_p]),
+    "pcv_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_void_p, c_int, c_void_p,
+                               c_double, c_double, c_double, c_double, c_double, c_double, c_int, c_void_p]),
 }
 
 

@@ -180,6 +180,12 @@ class Engine:
             stat = stat / self.world
         return stat[0], stat[1]
 
+    def apply_grads(self, optimizer, lr: Optional[float] = None) -> None:
+        """train_lm.py:316-353: clip + optimizer update from the (already averaged) gradients of the last
+        compute_grads / train_step; `optimizer` is a plaincv_b200.optim.AdamW.  The bf16 compute copies are
+        refreshed by the same kernel."""
+        optimizer.step(lr=lr)
+
     def after_optimizer_step(self) -> None:
         """Refresh the bf16 compute copies of the parameters (one cast kernel over the flat buffer)."""
         self.model.sync_compute_weights()

@@ -113,6 +113,29 @@ def cast_pad_bf16(src: torch.Tensor, dst: torch.Tensor, rows: int, cols: int, sr
           "pcv_cast_pad_bf16")
 
 
+def sumsq_partials(g: torch.Tensor, partials: torch.Tensor) -> None:
+    """partials[b] = this block's share of sum(g^2) (optax.global_norm inside _clip_grads, train_lm.py:173-178)."""
+    _req(g, torch.float32, "sumsq_partials")
+    _req(partials, torch.float32, "sumsq_partials")
+    check(_lib.load().pcv_sumsq_partials(g.data_ptr(), g.numel(), partials.data_ptr(), partials.numel(), _stream()),
+          "pcv_sumsq_partials")
+
+
+def adamw_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, p_bf16: Optional[torch.Tensor],
+               partials: Optional[torch.Tensor], norm_out: Optional[torch.Tensor], max_norm: float, lr: float, b1: float,
+               b2: float, eps: float, weight_decay: float, step: int) -> None:
+    """Clip + optax.adamw update of flat fp32 buffers in one pass (train_lm.py:173-178, 316-353;
+    optim/factory.py:193-205); p_bf16 receives the refreshed compute copy."""
+    for t in (p, g, m, v):
+        _req(t, torch.float32, "adamw_step")
+    check(_lib.load().pcv_adamw_step(
+        p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p_bf16.data_ptr() if p_bf16 is not None else None,
+        p.numel(), partials.data_ptr() if partials is not None else None,
+        partials.numel() if partials is not None else 0, norm_out.data_ptr() if norm_out is not None else None,
+        float(max_norm), float(lr), float(b1), float(b2), float(eps), float(weight_decay), int(step), _stream()),
+        "pcv_adamw_step")
+
+
 def embed_fwd(ids: torch.Tensor, table_bf16: torch.Tensor, d: int) -> torch.Tensor:
     M = ids.numel()
     x = torch.empty((M, d), dtype=torch.bfloat16, device=ids.device)

@@ -242,3 +242,35 @@ def test_softmax_ce(ops, M, V):
     buf = torch.zeros(M, ldl, dtype=torch.bfloat16).cuda()
     out2, _ = ops.softmax_ce(buf, labels.cuda(), V, 1.0, False)
     assert float(out2[0]) == pytest.approx(math.log(V), rel=1e-6)
+
+
+@pytest.mark.parametrize("n,max_norm", [(1 << 20, 1.0), (1000003, 0.05), (4099, None), (3 * 1024 * 1024 + 8, 100.0)])
+def test_clip_adamw_flat(ops, n, max_norm):
+    """pcv_sumsq_partials + pcv_adamw_step against the oracle's _clip_grads + optax.adamw restatement
+    (train_lm.py:173-178, 316-353; optim/factory.py:193-205) over three consecutive updates of one flat buffer;
+    fp32 state within 2e-6 relative (same formula, different association), the norm within 1e-6, and the bf16 compute
+    copy bit-identical to the rounding of the kernel's own fp32 parameters."""
+    g = torch.Generator().manual_seed(5)
+    p0 = torch.randn(n, generator=g) * 0.02
+    lr, b1, b2, eps, wd = 3e-3, 0.9, 0.999, 1e-8, 0.1
+    p_d, m_d, v_d = p0.cuda(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    pb = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    partials = torch.zeros(296, device="cuda")
+    norm_d = torch.zeros(1, device="cuda")
+    p_o = {"w": p0.clone()}
+    m_o, v_o = {"w": torch.zeros(n)}, {"w": torch.zeros(n)}
+    for step in (1, 2, 3):
+        gr = torch.randn(n, generator=g) * (0.5 if step == 2 else 0.003)
+        ops.sumsq_partials(gr.cuda(), partials)
+        ops.adamw_step(p_d, gr.cuda(), m_d, v_d, pb, partials if max_norm is not None else None, norm_d,
+                       max_norm if max_norm is not None else 0.0, lr, b1, b2, eps, wd, step)
+        gc = O.clip_grads({"w": gr}, max_norm)
+        p_o, m_o, v_o = O.adamw_step(p_o, gc, m_o, v_o, step, lr, b1, b2, eps, wd)
+        torch.cuda.synchronize()
+        if max_norm is not None:
+            assert abs(float(norm_d) - float(gr.double().norm())) <= 1e-6 * float(gr.double().norm())
+        assert rel_l2(p_d, p_o["w"]) < 2e-6
+        assert rel_l2(m_d, m_o["w"]) < 2e-6
+        assert rel_l2(v_d, v_o["w"]) < 2e-6
+        assert float((p_d.cpu() - p_o["w"]).abs().max()) < 1e-6
+        assert torch.equal(pb, p_d.to(torch.bfloat16))
