@@ -273,7 +273,11 @@ def gpu_main(args) -> None:
     c = CONFIGS[args.config]
     B, T, V = c["micro_batch"], c["seq_len"], c["vocab_size"]
     model, mcfg = construct_model(yaml_like_cfg(c), device=dev)
-    eng = Engine(model, seq_len=T, use_doc_mask=c["doc"])
+    # PCV_DDP_OVERLAP=0 (A/B runs only): all-reduce the buckets after backward instead of under it
+    # PCV_DDP_COMM=fp32 (A/B runs only): all-reduce the gradient buckets in fp32 instead of bf16
+    comm_fp32 = os.environ.get("PCV_DDP_COMM", "bf16") == "fp32"
+    eng = Engine(model, seq_len=T, use_doc_mask=c["doc"], overlap=os.environ.get("PCV_DDP_OVERLAP", "1") != "0",
+                 grad_comm_dtype=torch.float32 if comm_fp32 else torch.bfloat16)
     lib = _lib.load()
     tokens_per_step = B * T * world
 
@@ -348,7 +352,8 @@ def gpu_main(args) -> None:
                        "micro_batch_per_gpu": B, "parallelism": f"dp{world}", "params": model.count_params()[0],
                        "flop_per_token": fpt, "weights": "random-init (seed 100), fp32 masters + bf16 compute copies",
                        "l2": "working set per step (0.8 GB bf16 weights + ~13 GB activations at c3) >> 126 MB L2",
-                       "step": "zero grads + bf16 weight refresh + fwd + bwd + (N>1) bucketed fp32 all-reduce"},
+                       "step": "zero grads + bf16 weight refresh + fwd + bwd + (N>1) bucketed "
+                               + ("fp32" if comm_fp32 else "bf16") + " gradient all-reduce under backward"},
             "mfu": {"of_burst_peak": tok_s * fpt / (world * peaks["bf16_tflops"] * 1e12),
                     "of_sustained_peak": tok_s * fpt / (world * peaks["bf16_tflops_sustained"] * 1e12),
                     "peaks": peaks["_source"]},

@@ -121,6 +121,11 @@ int pcv_mean2(const float* row_loss, const float* row_correct, float* out, int M
 /* out[i] += in[i] (bf16), helper for gradient joins of the residual stream */
 int pcv_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
 
+/* Gradient buckets on their way to / from a bf16 all-reduce: to_bf16 = 1: dst(bf16)[i] = rn(src(fp32)[i]);
+ * to_bf16 = 0: dst(fp32)[i] = src(bf16)[i].  The data-parallel exchange replaces jax.lax.pmean(grads, "data")
+ * (train_lm.py:207, 268); the reduction itself is NCCL's. */
+int pcv_cast_f32_bf16(const void* src, void* dst, long long n, int to_bf16, void* stream);
+
 /* ---- the step after the hot path: global-norm clip + AdamW over flat fp32 buffers ----
  * partials[b] = sum of g[i]^2 over block b's share (n_partials blocks, fixed order: reproducible norm).
  * Replaces optax.global_norm in _clip_grads, train_lm.py:173-178. */

@@ -55,6 +55,7 @@ SIGNATURES = {
                                c_void_p]),
     "pcv_mean2": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "pcv_add_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_longlong, c_void_p]),
+    "pcv_cast_f32_bf16": (c_int, [c_void_p, c_void_p, c_longlong, c_int, c_void_p]),
     "pcv_sumsq_partials": (c_int, [c_void_p, c_longlong, c_void_p, c_int, c_void_p]),
     "pcv_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_void_p, c_int, c_void_p,
                                c_double, c_double, c_double, c_double, c_double, c_double, c_int, c_void_p]),

@@ -123,6 +123,37 @@ adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restri
   }
 }
 
+// Gradient buckets on their way to / from the all-reduce: fp32 -> bf16 (round to nearest even) and back.
+__global__ void __launch_bounds__(kOptThreads)
+cast_f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long n4, long n) {
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  uint2* d2 = reinterpret_cast<uint2*>(dst);
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const float4 a = __ldg(s4 + i);
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(a.x, a.y), hi = __floats2bfloat162_rn(a.z, a.w);
+    uint2 o;
+    o.x = *reinterpret_cast<const uint32_t*>(&lo);
+    o.y = *reinterpret_cast<const uint32_t*>(&hi);
+    d2[i] = o;
+  }
+  if (blockIdx.x == 0)
+    for (long i = n4 * 4 + threadIdx.x; i < n; i += blockDim.x) dst[i] = __float2bfloat16_rn(src[i]);
+}
+__global__ void __launch_bounds__(kOptThreads)
+cast_bf16_to_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, long n4, long n) {
+  const uint2* s2 = reinterpret_cast<const uint2*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const uint2 a = __ldg(s2 + i);
+    d4[i] = make_float4(__uint_as_float(a.x << 16), __uint_as_float(a.x & 0xffff0000u), __uint_as_float(a.y << 16),
+                        __uint_as_float(a.y & 0xffff0000u));
+  }
+  if (blockIdx.x == 0)
+    for (long i = n4 * 4 + threadIdx.x; i < n; i += blockDim.x) dst[i] = __bfloat162float(src[i]);
+}
+
 static bool al16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
 
 }  // namespace pcv
@@ -156,6 +187,27 @@ extern "C" int pcv_adamw_step(float* p, const float* g, float* m, float* v, void
   const int grid = num_sms() * 8;
   adamw_kernel<<<grid, kOptThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       p, g, m, v, static_cast<__nv_bfloat16*>(p_bf16), n / 4, n, partials, partials ? n_partials : 0, norm_out, a);
+  count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_cast_f32_bf16(const void* src, void* dst, long long n, int to_bf16, void* stream) {
+  using namespace pcv;
+  if (!src || !dst || n <= 0) return PCV_ERR_ARG;
+  // the vector body needs 16-byte aligned fp32 and 8-byte aligned bf16 addresses
+  const void* f = to_bf16 ? src : dst;
+  const void* b = to_bf16 ? dst : src;
+  if (!al16(f) || (reinterpret_cast<uintptr_t>(b) & 7)) return PCV_ERR_ALIGN;
+  long blocks = (n / 4 + kOptThreads - 1) / kOptThreads;
+  const long cap = static_cast<long>(num_sms()) * 8;
+  const int grid = static_cast<int>(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (to_bf16)
+    cast_f32_to_bf16_kernel<<<grid, kOptThreads, 0, st>>>(static_cast<const float*>(src),
+                                                          static_cast<__nv_bfloat16*>(dst), n / 4, n);
+  else
+    cast_bf16_to_f32_kernel<<<grid, kOptThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(src),
+                                                          static_cast<float*>(dst), n / 4, n);
   count_launch();
   return cuda_rc();
 }

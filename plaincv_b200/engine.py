@@ -25,8 +25,14 @@ class GradReducer:
     (fenced by events, so they overlap whatever the compute stream does next); with CPU tensors (gloo, used by the
     world_size=2 tests) they are issued as async work handles."""
 
-    def __init__(self, flat_grad: torch.Tensor, ranges: Sequence[Tuple[int, int]], process_group=None):
+    def __init__(self, flat_grad: torch.Tensor, ranges: Sequence[Tuple[int, int]], process_group=None,
+                 comm_dtype: torch.dtype = torch.float32):
+        """comm_dtype = torch.bfloat16 halves what crosses NVLink: a bucket is rounded to bf16 (round to nearest even),
+        all-reduced in bf16 and written back to the fp32 buffer.  torch.float32 is the reference's pmean precision."""
+        if comm_dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("comm_dtype must be torch.float32 or torch.bfloat16")
         self.flat = flat_grad
+        self.comm_dtype = comm_dtype
         self.ranges = list(ranges)
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
@@ -36,6 +42,9 @@ class GradReducer:
         self._launched: List[int] = []
         backend = dist.get_backend(process_group) if self.world > 1 else None
         self._avg_op = dist.ReduceOp.AVG if backend == "nccl" else None
+        self._wire = None
+        if self.world > 1 and comm_dtype == torch.bfloat16 and self.cuda:
+            self._wire = torch.empty(flat_grad.numel(), dtype=torch.bfloat16, device=flat_grad.device)
 
     def _all_reduce_mean(self, t: torch.Tensor, async_op: bool):
         if self._avg_op is not None:
@@ -55,9 +64,20 @@ class GradReducer:
             ev.record(torch.cuda.current_stream())
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
-                self._all_reduce_mean(view, async_op=False)
+                if self._wire is not None:
+                    from . import ops
+                    wire = self._wire[b:e]
+                    ops.cast_f32_bf16(view, wire)
+                    self._all_reduce_mean(wire, async_op=False)
+                    ops.cast_f32_bf16(wire, view)
+                else:
+                    self._all_reduce_mean(view, async_op=False)
         else:
-            self._handles.append(self._all_reduce_mean(view, async_op=True))
+            rounded = self.comm_dtype == torch.bfloat16
+            if rounded:
+                # CPU (gloo) runs of the host logic: same rounding points, the sum itself in fp32
+                view.copy_(view.to(torch.bfloat16).to(torch.float32))
+            self._handles.append((self._all_reduce_mean(view, async_op=True), view if rounded else None))
 
     def reduce_scalars(self, t: torch.Tensor) -> None:
         """Mean all-reduce of a small tensor (loss, acc) on the same path as the buckets."""
@@ -70,7 +90,7 @@ class GradReducer:
             with torch.cuda.stream(self.comm_stream):
                 self._all_reduce_mean(t, async_op=False)
         else:
-            self._handles.append(self._all_reduce_mean(t, async_op=True))
+            self._handles.append((self._all_reduce_mean(t, async_op=True), None))
 
     def finish(self) -> None:
         """Launch any bucket not yet launched, then make the compute stream wait for all of them."""
@@ -83,13 +103,15 @@ class GradReducer:
         if self.cuda:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         else:
-            for h in self._handles:
+            for h, round_back in self._handles:
                 if isinstance(h, tuple):
                     work, t = h
                     work.wait()
                     t.div_(self.world)
                 elif h is not None:
                     h.wait()
+                if round_back is not None:
+                    round_back.copy_(round_back.to(torch.bfloat16).to(torch.float32))
             self._handles = []
 
 
@@ -97,7 +119,7 @@ class Engine:
     """compute_grads / eval_step / train_step over a plaincv_b200.Transformer."""
 
     def __init__(self, model, seq_len: Optional[int] = None, use_doc_mask: bool = False, process_group=None,
-                 overlap: bool = True):
+                 overlap: bool = True, grad_comm_dtype: torch.dtype = torch.bfloat16):
         self.model = model
         self.seq_len = int(seq_len if seq_len is not None else model.cfg.seq_len)
         self.use_doc_mask = bool(use_doc_mask)
@@ -106,7 +128,7 @@ class Engine:
         L = model.layout
         # buckets in the order their gradients become final during backward: head, layers L-1..0, embedding
         self._ranges = [L.head_range] + list(reversed(L.layer_ranges)) + [L.embed_range]
-        self.reducer = GradReducer(model.flat_grad, self._ranges, process_group)
+        self.reducer = GradReducer(model.flat_grad, self._ranges, process_group, comm_dtype=grad_comm_dtype)
 
     # ------------------------------------------------------------------ hooks
     def _arm_hooks(self, on: bool) -> None:

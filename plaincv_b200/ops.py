@@ -113,6 +113,15 @@ def cast_pad_bf16(src: torch.Tensor, dst: torch.Tensor, rows: int, cols: int, sr
           "pcv_cast_pad_bf16")
 
 
+def cast_f32_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    """dst = src converted between fp32 and bf16 (flat, same numel), direction from the dtypes."""
+    to_bf16 = src.dtype == torch.float32
+    _req(src, torch.float32 if to_bf16 else torch.bfloat16, "cast_f32_bf16")
+    _req(dst, torch.bfloat16 if to_bf16 else torch.float32, "cast_f32_bf16")
+    check(_lib.load().pcv_cast_f32_bf16(src.data_ptr(), dst.data_ptr(), src.numel(), int(to_bf16), _stream()),
+          "pcv_cast_f32_bf16")
+
+
 def sumsq_partials(g: torch.Tensor, partials: torch.Tensor) -> None:
     """partials[b] = this block's share of sum(g^2) (optax.global_norm inside _clip_grads, train_lm.py:173-178)."""
     _req(g, torch.float32, "sumsq_partials")

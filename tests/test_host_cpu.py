@@ -200,6 +200,14 @@ def _ddp_worker(rank, world, port, q):
         flat.copy_(mine)
         red.finish()
         ok = ok and torch.allclose(flat, exp, atol=1e-6)
+        # bf16 on the wire: each rank's bucket is rounded to bf16, the mean is rounded again
+        flat.copy_(mine)
+        red16 = GradReducer(flat, ranges, comm_dtype=torch.bfloat16)
+        red16.bucket_ready(0)
+        red16.finish()
+        bf = lambda t: t.to(torch.bfloat16).to(torch.float32)  # noqa: E731
+        exp16 = bf(sum(bf(o) for o in others) / world)
+        ok = ok and torch.equal(flat, exp16) and float((flat - exp).abs().max()) < 2e-2
         # sharding: rank r takes the r-th contiguous slice of the global batch (train_lm.py:151-159)
         glob = torch.arange(8 * 5).view(8, 5)
         from plaincv_b200.batch import shard_for_rank
