@@ -118,6 +118,12 @@ int pcv_softmax_ce(const void* logits, const int32_t* labels, void* dlogits, flo
 /* out[0] = sum(row_loss)/M, out[1] = sum(row_correct)/M  (deterministic single-block reduction) */
 int pcv_mean2(const float* row_loss, const float* row_correct, float* out, int M, void* stream);
 
+/* Un-gated MLP activations over n = M * hid_pad bf16 elements.  mode 0: silu — MLP,
+ * models/LM/transformer.py:70-97; mode 1: relu(x)^2 — MLPReluSquared, transformer.py:138-165.
+ * fwd: h = act(x); bwd: dx = dh * act'(x).  fp32 math, bf16 in / out. */
+int pcv_act_fwd(const void* x, void* h, long long n, int mode, void* stream);
+int pcv_act_bwd(const void* x, const void* dh, void* dx, long long n, int mode, void* stream);
+
 /* out[i] += in[i] (bf16), helper for gradient joins of the residual stream */
 int pcv_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
 

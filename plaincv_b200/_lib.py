@@ -54,6 +54,8 @@ SIGNATURES = {
     "pcv_softmax_ce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                c_void_p]),
     "pcv_mean2": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "pcv_act_fwd": (c_int, [c_void_p, c_void_p, c_longlong, c_int, c_void_p]),
+    "pcv_act_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_longlong, c_int, c_void_p]),
     "pcv_add_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_longlong, c_void_p]),
     "pcv_cast_f32_bf16": (c_int, [c_void_p, c_void_p, c_longlong, c_int, c_void_p]),
     "pcv_sumsq_partials": (c_int, [c_void_p, c_longlong, c_void_p, c_int, c_void_p]),

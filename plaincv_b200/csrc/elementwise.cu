@@ -279,6 +279,45 @@ __global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ gu, const __
   }
 }
 
+// ---- un-gated MLP activations: MLP = silu(fc1 x) (transformer.py:70-97), MLPReluSquared =
+// relu(fc1 x)^2 (transformer.py:138-165).  mode 0: silu, 1: relu^2.  fp32 math on the bf16 Dense output, bf16 result.
+template <int MODE>
+__device__ __forceinline__ float act_fwd_elt(float x) {
+  if constexpr (MODE == 0) return x * sigmoid_fast(x);
+  const float r = fmaxf(x, 0.f);
+  return r * r;
+}
+template <int MODE>
+__device__ __forceinline__ float act_bwd_elt(float x, float dh) {
+  if constexpr (MODE == 0) {
+    const float s = sigmoid_fast(x);
+    return dh * (s + x * s * (1.f - s));
+  }
+  return dh * 2.f * fmaxf(x, 0.f);
+}
+template <int MODE, bool BWD>
+__global__ void act_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dh,
+                           __nv_bfloat16* __restrict__ out, long nvec) {
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < nvec;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    bf16x8 a, d;
+    a.raw = reinterpret_cast<const uint4*>(x)[i];
+    float fa[8], fd[8], o[8];
+    a.unpack(fa);
+    if constexpr (BWD) {
+      d.raw = reinterpret_cast<const uint4*>(dh)[i];
+      d.unpack(fd);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = act_bwd_elt<MODE>(fa[j], fd[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = act_fwd_elt<MODE>(fa[j]);
+    }
+    a.pack(o);
+    reinterpret_cast<uint4*>(out)[i] = a.raw;
+  }
+}
+
 __global__ void add_bf16_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
                                 __nv_bfloat16* __restrict__ out, long nvec) {
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < nvec;
@@ -415,6 +454,33 @@ extern "C" int pcv_swiglu_bwd(const void* gu, const void* dh, void* dgu, int M, 
   swiglu_bwd_kernel<<<ew_grid(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(gu), static_cast<const __nv_bfloat16*>(dh), static_cast<__nv_bfloat16*>(dgu), M,
       hid);
+  count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_act_fwd(const void* x, void* h, long long n, int mode, void* stream) {
+  if (!x || !h || n <= 0 || mode < 0 || mode > 1) return PCV_ERR_ARG;
+  if (n % 8 || !aligned16(x) || !aligned16(h)) return PCV_ERR_ALIGN;
+  const int grid = ew_grid(n / 8, 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* hp = static_cast<__nv_bfloat16*>(h);
+  if (mode == 0) act_kernel<0, false><<<grid, 256, 0, st>>>(xp, nullptr, hp, n / 8);
+  else act_kernel<1, false><<<grid, 256, 0, st>>>(xp, nullptr, hp, n / 8);
+  count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_act_bwd(const void* x, const void* dh, void* dx, long long n, int mode, void* stream) {
+  if (!x || !dh || !dx || n <= 0 || mode < 0 || mode > 1) return PCV_ERR_ARG;
+  if (n % 8 || !aligned16(x) || !aligned16(dh) || !aligned16(dx)) return PCV_ERR_ALIGN;
+  const int grid = ew_grid(n / 8, 256);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* dp = static_cast<const __nv_bfloat16*>(dh);
+  __nv_bfloat16* op = static_cast<__nv_bfloat16*>(dx);
+  if (mode == 0) act_kernel<0, true><<<grid, 256, 0, st>>>(xp, dp, op, n / 8);
+  else act_kernel<1, true><<<grid, 256, 0, st>>>(xp, dp, op, n / 8);
   count_launch();
   return cuda_rc();
 }

@@ -136,10 +136,10 @@ class ParamLayout:
     def __init__(self, cfg: ModelConfig):
         if cfg.dim % cfg.n_heads != 0:
             raise ValueError("dim must be divisible by n_heads")
-        if cfg.mlp != "glu":
-            raise NotImplementedError(f"mlp_class '{cfg.mlp}': only 'glu' runs on the B200 path in this round")
-        if cfg.tie_embeddings:
-            raise NotImplementedError("tie_embeddings=True is not on the B200 path in this round")
+        if cfg.mlp not in ("glu", "mlp", "mlp_relu_sq"):
+            raise ValueError(f"Unknown mlp type: {cfg.mlp}")  # transformer.py:332
+        self.gated = cfg.mlp == "glu"
+        self.tied = bool(cfg.tie_embeddings)
         d, hid, V = cfg.dim, cfg.hidden_dim, cfg.vocab_size
         self.d, self.hid, self.V = d, hid, V
         self.hid_pad, self.V_pad = _pad8(hid), _pad8(V)
@@ -155,7 +155,9 @@ class ParamLayout:
             self.slots[slot_name] = _Slot(off, rows, ld)
             off += (rows * ld + 127) // 128 * 128
 
-        add("embed", V, d)
+        # tied embeddings: the table doubles as the LM-head operand, so it gets the head's padded row count (pad rows
+        # stay zero: zero logits in the pad columns, exactly as with the padded lm_head kernel)
+        add("embed", self.V_pad if self.tied else V, d)
         self.views.append(_ParamView("embed_tokens/embedding", "embed", 0, 0, (V, d)))
         self.embed_range = (0, off)
         for i in range(cfg.n_layers):
@@ -165,7 +167,8 @@ class ParamLayout:
             add(f"{p}.w_qkv", d, 3 * d)
             add(f"{p}.w_out", d, d)
             add(f"{p}.mlp_norm", 1, d)
-            add(f"{p}.w_gu", d, 2 * self.hid_pad)
+            # glu: fc_gate | fc_up side by side (one GEMM); mlp / mlp_relu_sq: the slot holds fc1 alone
+            add(f"{p}.w_gu", d, (2 if self.gated else 1) * self.hid_pad)
             add(f"{p}.w_down", self.hid_pad, d)
             self.layer_ranges.append((begin, off))
             self.views += [
@@ -173,18 +176,20 @@ class ParamLayout:
                 _ParamView(f"{p}/attn/w_qkv/kernel", f"{p}.w_qkv", 0, 0, (d, 3 * d)),
                 _ParamView(f"{p}/attn/w_out/kernel", f"{p}.w_out", 0, 0, (d, d)),
                 _ParamView(f"{p}/mlp_norm/RMSNorm_0/scale", f"{p}.mlp_norm", 0, 0, (d,)),
-                _ParamView(f"{p}/mlp/fc_gate/kernel", f"{p}.w_gu", 0, 0, (d, hid)),
-                _ParamView(f"{p}/mlp/fc_up/kernel", f"{p}.w_gu", 0, self.hid_pad, (d, hid)),
-                _ParamView(f"{p}/mlp/fc2/kernel", f"{p}.w_down", 0, 0, (hid, d)),
             ]
+            if self.gated:
+                self.views += [_ParamView(f"{p}/mlp/fc_gate/kernel", f"{p}.w_gu", 0, 0, (d, hid)),
+                               _ParamView(f"{p}/mlp/fc_up/kernel", f"{p}.w_gu", 0, self.hid_pad, (d, hid))]
+            else:
+                self.views.append(_ParamView(f"{p}/mlp/fc1/kernel", f"{p}.w_gu", 0, 0, (d, hid)))
+            self.views.append(_ParamView(f"{p}/mlp/fc2/kernel", f"{p}.w_down", 0, 0, (hid, d)))
         begin = off
         add("out_norm", 1, d)
-        add("w_lm", d, self.V_pad)
+        self.views.append(_ParamView("out_norm/RMSNorm_0/scale", "out_norm", 0, 0, (d,)))
+        if not self.tied:  # tie_embeddings: logits = embed.attend(x) (transformer.py:394-396), no lm_head parameter
+            add("w_lm", d, self.V_pad)
+            self.views.append(_ParamView("lm_head/kernel", "w_lm", 0, 0, (d, V)))
         self.head_range = (begin, off)
-        self.views += [
-            _ParamView("out_norm/RMSNorm_0/scale", "out_norm", 0, 0, (d,)),
-            _ParamView("lm_head/kernel", "w_lm", 0, 0, (d, V)),
-        ]
         self.total = off
 
     def slot_view(self, flat: torch.Tensor, slot_name: str) -> torch.Tensor:
@@ -206,11 +211,11 @@ class _LayerHandles:
     """Raw tensors one block's kernels read/write (no nn.Module machinery on the hot path)."""
 
     __slots__ = ("attn_norm", "mlp_norm", "w_qkv", "w_out", "w_gu", "w_down", "g_attn_norm", "g_mlp_norm", "g_qkv",
-                 "g_out", "g_gu", "g_down", "on_grads_ready")
+                 "g_out", "g_gu", "g_down", "mlp", "on_grads_ready")
 
 
 class _HeadHandles:
-    __slots__ = ("out_norm", "w_lm", "g_out_norm", "g_lm", "vocab", "on_grads_ready")
+    __slots__ = ("out_norm", "w_lm", "g_out_norm", "g_lm", "vocab", "v_pad", "tied", "on_grads_ready")
 
 
 class _Runtime:
@@ -272,14 +277,21 @@ class Transformer(nn.Module):
             for short in ("qkv", "out", "gu", "down"):
                 setattr(h, f"w_{short}", L.slot_view(self.flat_bf16, f"{p}.w_{short}"))
                 setattr(h, f"g_{short}", L.slot_view(self.flat_grad, f"{p}.w_{short}"))
+            h.mlp = self.cfg.mlp
             h.on_grads_ready = None
             self.layers.append(h)
         hd = _HeadHandles()
         hd.out_norm = L.slot_view(self.flat_master, "out_norm").view(-1)
         hd.g_out_norm = L.slot_view(self.flat_grad, "out_norm").view(-1)
-        hd.w_lm = L.slot_view(self.flat_bf16, "w_lm")
-        hd.g_lm = L.slot_view(self.flat_grad, "w_lm")
+        hd.tied = L.tied
+        if L.tied:  # the LM head reads the embedding table [V, d] and adds its gradient to the table's
+            hd.w_lm = L.slot_view(self.flat_bf16, "embed")
+            hd.g_lm = L.slot_view(self.flat_grad, "embed")
+        else:
+            hd.w_lm = L.slot_view(self.flat_bf16, "w_lm")
+            hd.g_lm = L.slot_view(self.flat_grad, "w_lm")
         hd.vocab = self.cfg.vocab_size
+        hd.v_pad = L.V_pad
         hd.on_grads_ready = None
         self.head = hd
         self.embed_bf16 = L.slot_view(self.flat_bf16, "embed")
@@ -383,7 +395,13 @@ class Transformer(nn.Module):
         rt = self._runtime(B, T, doc_start)
         res, delta = self._trunk(ids, rt)
         res_f, hf = ops.RMSNormResidualFn.apply(res, delta, self.head.out_norm, self.head.g_out_norm, rt.eps)
-        logits = ops.LinearFn.apply(hf, self.head.w_lm, self.head.g_lm)
+        if self.head.tied:
+            if torch.is_grad_enabled() and res.requires_grad:
+                raise NotImplementedError("tie_embeddings: differentiate through loss_and_acc (the fused head), "
+                                          "module(input_ids) returns logits for inference only")
+            logits = ops.head_logits(hf, self.head)
+        else:
+            logits = ops.LinearFn.apply(hf, self.head.w_lm, self.head.g_lm)
         return logits.view(B, T, self.layout.V_pad)[:, :, : self.cfg.vocab_size]
 
     def loss_and_acc(self, input_ids: torch.Tensor, labels: torch.Tensor, *,

@@ -195,6 +195,54 @@ def swiglu_bwd(gu: torch.Tensor, dh: torch.Tensor) -> torch.Tensor:
     return dgu
 
 
+_ACT_MODE = {"mlp": 0, "mlp_relu_sq": 1}
+
+
+def act_fwd(x: torch.Tensor, mlp: str) -> torch.Tensor:
+    """h = silu(x) (MLP, transformer.py:70-97) or relu(x)^2 (MLPReluSquared, :138-165) on a bf16 Dense output."""
+    h = torch.empty_like(x)
+    check(_lib.load().pcv_act_fwd(x.data_ptr(), h.data_ptr(), x.numel(), _ACT_MODE[mlp], _stream()), "pcv_act_fwd")
+    return h
+
+
+def act_bwd(x: torch.Tensor, dh: torch.Tensor, mlp: str) -> torch.Tensor:
+    dx = torch.empty_like(x)
+    check(_lib.load().pcv_act_bwd(x.data_ptr(), dh.data_ptr(), dx.data_ptr(), x.numel(), _ACT_MODE[mlp], _stream()),
+          "pcv_act_bwd")
+    return dx
+
+
+def head_logits(hf: torch.Tensor, head) -> torch.Tensor:
+    """logits[M, V_pad] of the LM head: hf @ lm_head/kernel, or hf @ embedding^T when the embeddings are tied
+    (embed.attend, transformer.py:394-396: the table [V, d] is the K-major B operand as it lies)."""
+    if not head.tied:
+        return linear_fwd(hf, head.w_lm)
+    M, d = hf.shape
+    logits = torch.empty((M, head.v_pad), dtype=torch.bfloat16, device=hf.device)
+    gemm(hf, head.w_lm, logits, M, head.v_pad, d, d, d, head.v_pad, False, False, PCV_EPI_BF16)
+    return logits
+
+
+def head_dgrad(dlogits: torch.Tensor, head, alpha: float) -> torch.Tensor:
+    if not head.tied:
+        return linear_dgrad(dlogits, head.w_lm, alpha)
+    M = dlogits.shape[0]
+    d = head.w_lm.shape[1]
+    dx = torch.empty((M, d), dtype=torch.bfloat16, device=dlogits.device)
+    # dx[M, d] = dlogits[M, V] @ E[V, d]: B(n = d, k = V) is the table read MN-major
+    gemm(dlogits, head.w_lm, dx, M, d, head.v_pad, head.v_pad, d, d, False, True, PCV_EPI_BF16, 1, alpha)
+    return dx
+
+
+def head_wgrad(hf: torch.Tensor, dlogits: torch.Tensor, head, alpha: float) -> None:
+    if not head.tied:
+        linear_wgrad(hf, dlogits, head.g_lm, alpha)
+        return
+    # dE[V, d] += dlogits[M, V]^T @ hf[M, d]  (added to the gather's scatter-add in the same fp32 rows)
+    M, d = hf.shape
+    gemm(dlogits, hf, head.g_lm, head.v_pad, d, M, head.v_pad, d, d, True, True, PCV_EPI_F32_ATOMIC, 0, alpha)
+
+
 def attn_fwd(qkv: torch.Tensor, doc_start: Optional[torch.Tensor], B: int, T: int,
              n_heads: int) -> Tuple[torch.Tensor, torch.Tensor]:
     """qkv: q and k columns already rotated (linear_fwd_rope / rope_qk_)."""
@@ -402,7 +450,11 @@ class BlockFn(torch.autograd.Function):
         a = linear_fwd(o, layer.w_out)
         res2, h2, rstd2 = rmsnorm_residual_fwd(res1, a, layer.mlp_norm, eps)
         del a
-        gu, hh = linear_fwd_swiglu(h2, layer.w_gu)
+        if layer.mlp == "glu":
+            gu, hh = linear_fwd_swiglu(h2, layer.w_gu)
+        else:  # MLP / MLPReluSquared: gu holds fc1's output alone
+            gu = linear_fwd(h2, layer.w_gu)
+            hh = act_fwd(gu, layer.mlp)
         m = linear_fwd(hh, layer.w_down)
         ctx.save_for_backward(res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh)
         ctx.layer, ctx.rt, ctx.has_delta = layer, rt, delta is not None
@@ -416,7 +468,10 @@ class BlockFn(torch.autograd.Function):
         # MLP branch
         wg = wgrad_stream
         wg.launch(hh, d_m, layer.g_down)
-        d_gu = linear_dgrad_dswiglu(d_m, layer.w_down, gu)
+        if layer.mlp == "glu":
+            d_gu = linear_dgrad_dswiglu(d_m, layer.w_down, gu)
+        else:
+            d_gu = act_bwd(gu, linear_dgrad(d_m, layer.w_down), layer.mlp)
         wg.launch(h2, d_gu, layer.g_gu)
         d_h2 = linear_dgrad(d_gu, layer.w_gu)
         del d_gu
@@ -445,7 +500,7 @@ class HeadLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, res, delta, labels, head, rt, loss_scale, unit_grad):
         res_f, hf, rstd = rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
-        logits = linear_fwd(hf, head.w_lm)
+        logits = head_logits(hf, head)
         M = logits.shape[0]
         need_grad = bool(ctx.needs_input_grad[0])
         out2, dlogits = softmax_ce(logits, labels, head.vocab, loss_scale / M, need_grad)
@@ -459,8 +514,11 @@ class HeadLossFn(torch.autograd.Function):
         res_f, rstd, hf, dlogits = ctx.saved_tensors
         head = ctx.head
         alpha = 1.0 if ctx.unit_grad else float(g_out[0])
-        wgrad_stream.launch(hf, dlogits, head.g_lm, alpha)
-        d_hf = linear_dgrad(dlogits, head.w_lm, alpha)
+        if head.tied:
+            head_wgrad(hf, dlogits, head, alpha)
+        else:
+            wgrad_stream.launch(hf, dlogits, head.g_lm, alpha)
+        d_hf = head_dgrad(dlogits, head, alpha)
         d_r = rmsnorm_residual_bwd(d_hf, None, res_f, head.out_norm, rstd, head.g_out_norm)
         wgrad_stream.join(d_r.device)
         if head.on_grads_ready is not None:

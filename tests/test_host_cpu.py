@@ -97,8 +97,22 @@ def test_param_layout_mirrors_flax_tree():
     ranges = [L.embed_range] + L.layer_ranges + [L.head_range]
     assert ranges[0][0] == 0 and ranges[-1][1] == L.total
     assert all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))
-    with pytest.raises(NotImplementedError):
-        ParamLayout(ModelConfig(vocab_size=8, seq_len=8, dim=64, expand=2.0, n_layers=1, n_heads=1, mlp="mlp"))
+    with pytest.raises(ValueError):  # transformer.py:332
+        ParamLayout(ModelConfig(vocab_size=8, seq_len=8, dim=64, expand=2.0, n_layers=1, n_heads=1, mlp="gelu"))
+    # SURVEY §8f N2 variants: fc1 alone in the gate|up slot, no lm_head parameter when the embeddings are tied
+    for mlp, tied in (("mlp", False), ("mlp_relu_sq", True), ("glu", True)):
+        cfg_v = ModelConfig(vocab_size=50257, seq_len=64, dim=128, expand=8 / 3, n_layers=2, n_heads=2, mlp=mlp,
+                            tie_embeddings=tied)
+        Lv = ParamLayout(cfg_v)
+        cfg_ov = O.ModelConfig(vocab_size=50257, seq_len=64, dim=128, expand=8 / 3, n_layers=2, n_heads=2, mlp=mlp,
+                               tie_embeddings=tied)
+        shapes_v = O.param_shapes(cfg_ov)
+        assert {v.name: v.shape for v in Lv.views} == shapes_v
+        flat_v = torch.zeros(Lv.total)
+        for v in Lv.views:
+            Lv.param_view(flat_v, v).add_(1.0)
+        assert float(flat_v.max()) == 1.0 and int(flat_v.sum()) == sum(int(np.prod(s)) for s in shapes_v.values())
+        assert Lv.slots["embed"].rows == (Lv.V_pad if tied else 50257)
     with pytest.raises(NotImplementedError):
         model_config_from_cfg(dict(model="pythia"))
     with pytest.raises(ValueError):

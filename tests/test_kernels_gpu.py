@@ -274,3 +274,22 @@ def test_clip_adamw_flat(ops, n, max_norm):
         assert rel_l2(v_d, v_o["w"]) < 2e-6
         assert float((p_d.cpu() - p_o["w"]).abs().max()) < 1e-6
         assert torch.equal(pb, p_d.to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("mlp", ["mlp", "mlp_relu_sq"])
+@pytest.mark.parametrize("M,hid", [(512, 2736), (300, 688)])
+def test_ungated_activations(ops, mlp, M, hid):
+    """pcv_act_fwd / pcv_act_bwd: silu (MLP, transformer.py:70-97) and relu^2 (MLPReluSquared,
+    :138-165) of a bf16 Dense output against the oracle's fp32 functions and their autograd transposes."""
+    g = torch.Generator().manual_seed(31)
+    x = _bf(torch.randn(M, hid, generator=g) * 1.5)
+    dh = _bf(torch.randn(M, hid, generator=g))
+    h = ops.act_fwd(x.cuda(), mlp)
+    dx = ops.act_bwd(x.cuda(), dh.cuda(), mlp)
+    xl = x.float().requires_grad_(True)
+    ref = O.silu(xl) if mlp == "mlp" else torch.square(torch.relu(xl))
+    ref.backward(dh.float())
+    assert rel_l2(h, ref) < 4e-3
+    assert rel_l2(dx, xl.grad) < 4e-3
+    if mlp == "mlp_relu_sq":  # exact where the input is non-positive
+        assert float(h.cpu()[x <= 0].abs().max()) == 0.0 and float(dx.cpu()[x <= 0].abs().max()) == 0.0

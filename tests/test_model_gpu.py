@@ -19,7 +19,8 @@ def rel_l2(a, b):
 def _build(cfg_o, seed=0):
     from plaincv_b200.model import ModelConfig, Transformer
     cfg = ModelConfig(vocab_size=cfg_o.vocab_size, seq_len=cfg_o.seq_len, dim=cfg_o.dim, expand=cfg_o.expand,
-                      n_layers=cfg_o.n_layers, n_heads=cfg_o.n_heads, mlp=cfg_o.mlp, rope_theta=cfg_o.rope_theta)
+                      n_layers=cfg_o.n_layers, n_heads=cfg_o.n_heads, mlp=cfg_o.mlp, rope_theta=cfg_o.rope_theta,
+                      tie_embeddings=cfg_o.tie_embeddings)
     model = Transformer(cfg, device="cuda", seed=seed)
     params = O.init_params(cfg_o, seed=seed)
     model.load_flax_params(params)
@@ -59,6 +60,23 @@ def test_c1_tiny_config_parity():
     model, params = _build(cfg_o)
     batch = O.synthetic_batch(8, 256, 50257, seed=1234)
     _compare(model, params, cfg_o, batch, False)
+
+
+@pytest.mark.parametrize("mlp,tied,vocab", [("mlp", False, 1000), ("mlp_relu_sq", False, 1003), ("glu", True, 1003),
+                                            ("mlp", True, 50257)])
+def test_model_variants_parity(mlp, tied, vocab):
+    """the MLP / MLPReluSquared blocks (transformer.py:70-97, 138-165) and tied embeddings
+    (embed.attend, :394-396 — the table's gradient is the gather's scatter-add plus the head's weight gradient), loss
+    and every parameter gradient against the fp32 oracle at the whole-path tolerances."""
+    cfg_o = O.ModelConfig(vocab_size=vocab, seq_len=256, dim=128, expand=8 / 3, n_layers=2, n_heads=2, mlp=mlp,
+                          tie_embeddings=tied)
+    model, params = _build(cfg_o)
+    assert ("lm_head/kernel" in params) == (not tied)
+    batch = O.synthetic_batch(4, 256, vocab, seed=11, doc_mean=None)
+    _compare(model, params, cfg_o, batch, use_doc=False)
+    L = model.layout
+    if tied:  # pad rows of the table (vocab -> multiple of 8) receive no gradient
+        assert float(L.slot_view(model.flat_grad, "embed")[vocab:].abs().sum()) == 0.0
 
 
 def test_doc_masked_parity():
