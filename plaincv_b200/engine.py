@@ -144,7 +144,11 @@ class Engine:
                 layer.on_grads_ready = None
 
     # ------------------------------------------------------------------ steps
-    def _to_device(self, batch: dict):
+    def _to_device(self, batch):
+        if hasattr(batch, "inputs") and hasattr(batch, "labels"):  # a feed.DeviceBatch: already prepared and staged
+            if self.use_doc_mask and batch.doc_start is None:
+                raise ValueError("Doc masking enabled but batch has no 'docs_lengths'.")  # train_lm.py:110
+            return batch.inputs, batch.labels, (batch.doc_start if self.use_doc_mask else None)
         inputs, labels, doc_start = prepare_batch(batch, self.seq_len, self.use_doc_mask)
         dev = self.model.flat_grad.device
 
