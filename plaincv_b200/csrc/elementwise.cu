@@ -246,7 +246,11 @@ __global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfl
     g.unpack(fg);
     u.unpack(fu);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = swiglu_fwd_elt(fg[j], fu[j]);
+    for (int j = 0; j < 8; j += 2) {
+      const float2 h2 = swiglu_fwd_pair(make_float2(fg[j], fg[j + 1]), make_float2(fu[j], fu[j + 1]));
+      o[j] = h2.x;
+      o[j + 1] = h2.y;
+    }
     bf16x8 w;
     w.pack(o);
     *reinterpret_cast<uint4*>(h + r * hid + c) = w.raw;
@@ -270,7 +274,12 @@ __global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ gu, const __
     u.unpack(fu);
     d.unpack(fd);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) swiglu_bwd_elt(fg[j], fu[j], fd[j], og[j], ou[j]);
+    for (int j = 0; j < 8; j += 2) {
+      float2 dg, du;
+      swiglu_bwd_pair(make_float2(fg[j], fg[j + 1]), make_float2(fu[j], fu[j + 1]), make_float2(fd[j], fd[j + 1]), dg, du);
+      og[j] = dg.x; og[j + 1] = dg.y;
+      ou[j] = du.x; ou[j + 1] = du.y;
+    }
     bf16x8 wg, wu;
     wg.pack(og);
     wu.pack(ou);

@@ -236,8 +236,8 @@ __device__ __forceinline__ void swiglu32(const uint32_t* g, const uint32_t* u, u
     for (int k = 0; k < 4; ++k) {
       gw[k] = pack_bf16x2(__uint_as_float(g[v * 8 + 2 * k]), __uint_as_float(g[v * 8 + 2 * k + 1]));
       uw[k] = pack_bf16x2(__uint_as_float(u[v * 8 + 2 * k]), __uint_as_float(u[v * 8 + 2 * k + 1]));
-      const float2 fg = unpack_bf16x2(gw[k]), fu = unpack_bf16x2(uw[k]);
-      hw[k] = pack_bf16x2(swiglu_fwd_elt(fg.x, fu.x), swiglu_fwd_elt(fg.y, fu.y));
+      const float2 fh = swiglu_fwd_pair(unpack_bf16x2(gw[k]), unpack_bf16x2(uw[k]));
+      hw[k] = pack_bf16x2(fh.x, fh.y);
     }
   }
 }
@@ -250,14 +250,13 @@ __device__ __forceinline__ void dswiglu32(const uint32_t* r, float alpha, uint4*
     uint32_t* uw = reinterpret_cast<uint32_t*>(&qu[v]);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float2 fd = unpack_bf16x2(pack_bf16x2(__uint_as_float(r[v * 8 + 2 * k]) * alpha,
-                                                  __uint_as_float(r[v * 8 + 2 * k + 1]) * alpha));
-      const float2 fg = unpack_bf16x2(gw[k]), fu = unpack_bf16x2(uw[k]);
-      float dg0, du0, dg1, du1;
-      swiglu_bwd_elt(fg.x, fu.x, fd.x, dg0, du0);
-      swiglu_bwd_elt(fg.y, fu.y, fd.y, dg1, du1);
-      gw[k] = pack_bf16x2(dg0, dg1);
-      uw[k] = pack_bf16x2(du0, du1);
+      const float2 acc = __fmul2_rn(make_float2(__uint_as_float(r[v * 8 + 2 * k]), __uint_as_float(r[v * 8 + 2 * k + 1])),
+                                    make_float2(alpha, alpha));
+      const float2 fd = unpack_bf16x2(pack_bf16x2(acc.x, acc.y));
+      float2 dg, du;
+      swiglu_bwd_pair(unpack_bf16x2(gw[k]), unpack_bf16x2(uw[k]), fd, dg, du);
+      gw[k] = pack_bf16x2(dg.x, dg.y);
+      uw[k] = pack_bf16x2(du.x, du.y);
     }
   }
 }

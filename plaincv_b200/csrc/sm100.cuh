@@ -327,4 +327,28 @@ __device__ __forceinline__ void swiglu_bwd_elt(float g, float u, float dh, float
   dg = dh * u * (s + silu * (1.f - s));
 }
 
+// The same on two elements at a time with the packed fp32x2 instructions of sm_100 (one issue slot per pair for every
+// multiply / add / fma; the four MUFU ops stay scalar).  Explicit round-to-nearest intrinsics fix the operation
+// sequence, so the stand-alone SwiGLU kernels and the fused GEMM epilogues — both built from these — agree bit for bit.
+__device__ __forceinline__ float2 sigmoid_fast2(float2 g) {
+  const float2 t = __fmul2_rn(g, make_float2(-1.4426950408889634f, -1.4426950408889634f));
+  float e0, e1, s0, s1;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(t.x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(t.y));
+  const float2 den = __fadd2_rn(make_float2(e0, e1), make_float2(1.f, 1.f));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s0) : "f"(den.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s1) : "f"(den.y));
+  return make_float2(s0, s1);
+}
+__device__ __forceinline__ float2 swiglu_fwd_pair(float2 g, float2 u) {
+  return __fmul2_rn(__fmul2_rn(g, sigmoid_fast2(g)), u);
+}
+__device__ __forceinline__ void swiglu_bwd_pair(float2 g, float2 u, float2 dh, float2& dg, float2& du) {
+  const float2 s = sigmoid_fast2(g);
+  const float2 silu = __fmul2_rn(g, s);
+  du = __fmul2_rn(dh, silu);
+  const float2 oms = __ffma2_rn(s, make_float2(-1.f, -1.f), make_float2(1.f, 1.f));
+  dg = __fmul2_rn(__fmul2_rn(dh, u), __ffma2_rn(silu, oms, s));
+}
+
 }  // namespace pcv
