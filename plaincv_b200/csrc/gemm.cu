@@ -692,6 +692,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           if (nsl == 0) nsl = 1;
           else { nsl = 0; nw += npairs; }
           if (seek(nw, nsl, nc, nr) && lane == 0) request(nc, nr);
+          if (prof) { const unsigned int t = clk32(); pf1 += t - pt; pt = t; }  // lds + issue of the next slab's loads
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             uint32_t r[32];

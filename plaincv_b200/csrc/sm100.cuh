@@ -331,6 +331,14 @@ __device__ __forceinline__ void swiglu_bwd_elt(float g, float u, float dh, float
 // multiply / add / fma; the four MUFU ops stay scalar).  Explicit round-to-nearest intrinsics fix the operation
 // sequence, so the stand-alone SwiGLU kernels and the fused GEMM epilogues — both built from these — agree bit for bit.
 __device__ __forceinline__ float2 sigmoid_fast2(float2 g) {
+#ifdef PCV_SIGMOID_TANH
+  // sigmoid(g) = 0.5 tanh(g / 2) + 0.5: one MUFU op per element instead of two
+  const float2 t = __fmul2_rn(g, make_float2(0.5f, 0.5f));
+  float h0, h1;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(h0) : "f"(t.x));
+  asm("tanh.approx.f32 %0, %1;" : "=f"(h1) : "f"(t.y));
+  return __ffma2_rn(make_float2(h0, h1), make_float2(0.5f, 0.5f), make_float2(0.5f, 0.5f));
+#else
   const float2 t = __fmul2_rn(g, make_float2(-1.4426950408889634f, -1.4426950408889634f));
   float e0, e1, s0, s1;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(t.x));
@@ -339,6 +347,7 @@ __device__ __forceinline__ float2 sigmoid_fast2(float2 g) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s0) : "f"(den.x));
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s1) : "f"(den.y));
   return make_float2(s0, s1);
+#endif
 }
 __device__ __forceinline__ float2 swiglu_fwd_pair(float2 g, float2 u) {
   return __fmul2_rn(__fmul2_rn(g, sigmoid_fast2(g)), u);
