@@ -613,7 +613,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       for (int v = 0; v < 8; ++v) st_shared_v4(bx + lane * 128 + ((v ^ sw) << 4), q[v]);
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
+      if (lane == 0 && !(p.dbg & 32)) {
         if constexpr (EPI == PCV_EPI_F32_ATOMIC) tma_reduce_add_2d(m, bx, c0, r0);
         else tma_store_2d(m, bx, c0, r0);
         tma_store_commit();

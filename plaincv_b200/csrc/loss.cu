@@ -65,7 +65,9 @@ softmax_ce_kernel(const __nv_bfloat16* __restrict__ logits, const int32_t* __res
         f[2 * j] = t.x;
         f[2 * j + 1] = t.y;
       }
-      if (v * 8 + 8 > V) {  // ragged last vector: neutralise the pad columns
+      if (v * 8 >= V) continue;  // a vector of nothing but pad columns (the pad may be wider than one vector)
+      if (v * 8 + 8 > V) {       // ragged last vector: neutralise the pad columns (it holds at least one real logit,
+                                 // so m is finite below and exp2(-FLT_MAX * log2e - mb) = 0)
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           if (v * 8 + j >= V) f[j] = -FLT_MAX;

@@ -83,8 +83,8 @@ def test_param_layout_mirrors_flax_tree():
     ocfg = O.ModelConfig(vocab_size=50257, seq_len=256, dim=256, expand=8 / 3, n_layers=4, n_heads=4)
     shapes = O.param_shapes(ocfg)
     assert {v.name: tuple(v.shape) for v in L.views} == shapes
-    # TMA rule: every padded row stride is a multiple of 16 bytes in bf16; slots start 256-byte aligned
-    assert L.hid_pad % 8 == 0 and L.V_pad % 8 == 0 and L.hid_pad >= 682 and L.V_pad >= 50257
+    # every padded activation row stride is a whole number of 128-byte lines in bf16; slots start 256-byte aligned
+    assert L.hid_pad % 64 == 0 and L.V_pad % 64 == 0 and L.hid_pad >= 682 and L.V_pad >= 50257
     for s in L.slots.values():
         assert (s.ld * 2) % 16 == 0 and (s.offset * 2) % 256 == 0
     # views of distinct parameters never overlap, and pad lanes belong to nobody

@@ -220,11 +220,12 @@ def test_attention_first_row_is_v0(ops):
     assert torch.equal(out.cpu(), qkv[:, 2 * d:])  # each row returns exactly its own v
 
 
-@pytest.mark.parametrize("M,V", [(256, 50257), (512, 50280), (128, 1000)])
+@pytest.mark.parametrize("M,V", [(256, 50257), (512, 50280), (128, 1000), (64, 1003)])
 def test_softmax_ce(ops, M, V):
     g = torch.Generator().manual_seed(7)
-    ldl = (V + 7) // 8 * 8
+    ldl = (V + 63) // 64 * 64  # the layout's row stride (model._pad64); pad columns hold garbage the kernel must ignore
     logits = _bf(torch.randn(M, ldl, generator=g) * 3)
+    logits[:, V:] = 1e4
     labels = torch.randint(0, V, (M,), generator=g, dtype=torch.int32)
     logits[5, labels[5]] = 40.0  # a confidently-correct row
     l32 = logits[:, :V].float().requires_grad_(True)

@@ -237,7 +237,7 @@ def test_full_size_properties_c3_shapes():
     # rounding noise itself (measured 3.6e-4 .. 4.0e-4 on the whole buffer, tools/repeat_check.py) — an order of
     # magnitude inside the parity tolerance, and the loss (forward only: no atomics) is bit-identical
     assert rel_l2(model.flat_grad, g_all) < 1e-3
-    # pad lanes of the flat buffers (hid 2730 -> 2736) stay exactly zero through forward and backward
+    # pad lanes of the flat buffers (hid 2730 -> 2752) stay exactly zero through forward and backward
     L = model.layout
     gu = L.slot_view(model.flat_grad, "layers_0.w_gu")
     assert float(gu[:, L.hid:L.hid_pad].abs().max()) == 0.0 and float(gu[:, L.hid_pad + L.hid:].abs().max()) == 0.0

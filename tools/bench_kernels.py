@@ -11,7 +11,7 @@ from plaincv_b200 import ops  # noqa: E402
 
 dev = "cuda"
 bf = torch.bfloat16
-B, T, NH, d, hp, Vp = 8, 2048, 16, 1024, int(os.environ.get("PCV_KB_HP", 2736)), 50280
+B, T, NH, d, hp, Vp = 8, 2048, 16, 1024, int(os.environ.get("PCV_KB_HP", 2752)), int(os.environ.get("PCV_KB_VP", 50304))
 if len(sys.argv) > 1:
     T = int(sys.argv[1])
     B = 16384 // T

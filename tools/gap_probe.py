@@ -6,7 +6,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from plaincv_b200 import ops
 dev = "cuda"; bf = torch.bfloat16
-M, d, hp = 16384, 1024, 2736
+M, d, hp = 16384, 1024, 2752
 x = torch.randn(M, d, device=dev).to(bf); dl = torch.randn(M, d, device=dev).to(bf)
 scale = torch.ones(d, device=dev)
 wo = (torch.randn(d, d, device=dev) * 0.02).to(bf)

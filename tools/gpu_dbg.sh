@@ -1,21 +1,2 @@
 #!/bin/bash
-# A/B: sigmoid through tanh.approx (one MUFU) instead of ex2 + rcp (two) in the SwiGLU math
-cp plaincv_b200/lib/libplaincv_b200.so /tmp/lib_base.so
-PCV_KB_CUBLAS=0 timeout 120 python tools/bench_kernels.py 2048 fused 2>&1 | grep "#1" | grep "swiglu"
-cp tools/libpcv_tanh.so plaincv_b200/lib/libplaincv_b200.so
-echo "--- tanh"
-PCV_KB_CUBLAS=0 timeout 120 python tools/bench_kernels.py 2048 fused 2>&1 | grep "#1" | grep "swiglu"
-timeout 600 python -m pytest tests/test_kernels_gpu.py tests/test_model_gpu.py -m gpu -x -q -k "swiglu or c1_tiny or golden" 2>&1 | tail -3
-python - <<'PY'
-import torch
-from plaincv_b200 import ops
-g = torch.linspace(-12, 12, 4097).repeat(8, 1).contiguous()
-u = torch.ones_like(g)
-gu = torch.cat([g, u], dim=1).to(torch.bfloat16).cuda()
-gu = torch.nn.functional.pad(gu, (0, 0))  # [8, 8194] -> need hid % 8: use 4096 cols
-g = g[:, :4096]; gu = torch.cat([g, torch.ones_like(g)], 1).to(torch.bfloat16).cuda().contiguous()
-h = ops.swiglu_fwd(gu).float().cpu()
-ref = torch.nn.functional.silu(g.to(torch.bfloat16).float())
-print("silu via tanh: max abs err %.3e, max rel err where |ref|>1e-2: %.3e" % (float((h - ref).abs().max()), float(((h - ref).abs() / ref.abs())[ref.abs() > 1e-2].max())))
-PY
-cp /tmp/lib_base.so plaincv_b200/lib/libplaincv_b200.so
+timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -4

@@ -11,7 +11,7 @@ from plaincv_b200 import _lib, ops  # noqa: E402
 
 dev = "cuda"
 bf = torch.bfloat16
-M, d, hp = 16384, 1024, 2736
+M, d, hp = 16384, 1024, 2752
 lib = _lib.load()
 buf = torch.zeros(148 * 8 * 8, dtype=torch.int32, device=dev)
 xg = torch.randn(M, d, device=dev).to(bf)
