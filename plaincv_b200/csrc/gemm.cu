@@ -423,22 +423,31 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 //   accumulate into both CTAs' tensor memory (128 lanes each); each CTA's epilogue warps drain their own half.
 // Per k-block a CTA pulls 32 KB for 2*128*256*64 flop: 128 flop per L2 byte against 85 for the single-CTA
 // 128 x 256 tile — the single-CTA kernel saturates the L2 -> SM fabric (~12 TB/s) near 1.1 PFLOP/s.
+#ifndef PCV_SWIGLU_BOXES
+#define PCV_SWIGLU_BOXES 1
+#endif
+#ifndef PCV_DSWIGLU_STAGES
+#define PCV_DSWIGLU_STAGES 4
+#endif
 constexpr bool pair_epi_fused(int epi) { return epi == EPI_SWIGLU || epi == EPI_DSWIGLU; }
 template <int EPI>
 struct PairCfgT {
   static constexpr bool kFused = pair_epi_fused(EPI);  // SwiGLU forward / backward in the epilogue
   static constexpr int kBN = 256;
   static constexpr int kTileM = 256;
-  // the fused epilogues trade one pipeline stage for a second 4 KB box per epilogue warp (two stores in flight, or the
-  // saved gate and up slabs of the SwiGLU backward brought in by TMA while the previous slab is still being worked on)
-  static constexpr int kStages = EPI == EPI_DSWIGLU ? 4 : (kFused ? 5 : 6);
+  // SwiGLU forward keeps all six stages and one box per epilogue warp: its epilogue has slack (the warps wait for the
+  // accumulator ~40 % of the time), while the ring feeds a mainloop that already runs at the L2 -> SM limit and has
+  // to absorb the epilogue's store traffic (6 stages / 1 box: 142 us, 5 stages / 2 boxes: 150 us at the 420M shape).
+  // SwiGLU backward gives up two stages for three boxes: the saved gate and up slabs arrive by TMA while the previous
+  // slab is still being worked on, and dg / du leave through the third
+  static constexpr int kStages = EPI == EPI_DSWIGLU ? PCV_DSWIGLU_STAGES : (kFused ? (PCV_SWIGLU_BOXES == 1 ? 6 : 5) : 6);
   static constexpr int kABytes = 128 * kBK * 2;  // this CTA's 128 rows of A
   static constexpr int kBBytes = 128 * kBK * 2;  // this CTA's 128 of the 256 B rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kBarBytes = 256;
   static constexpr int kEpiWarps = 8;
   static constexpr int kEpiBoxBytes = 32 * 128;  // 32 rows x 128 B (one 128B-swizzled TMA box)
-  static constexpr int kEpiBoxes = EPI == EPI_DSWIGLU ? 3 : (kFused ? 2 : 1);
+  static constexpr int kEpiBoxes = EPI == EPI_DSWIGLU ? 3 : (kFused ? PCV_SWIGLU_BOXES : 1);
   static constexpr int kEpiBufBytes = kEpiBoxes * kEpiBoxBytes;  // per epilogue warp
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kEpiBufBytes + kBarBytes + 1024;
   static constexpr uint32_t kTmemCols = 512;  // two 256-column accumulators

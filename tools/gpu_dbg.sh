@@ -1,2 +1,3 @@
 #!/bin/bash
-timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+PCV_KB_CUBLAS=0 timeout 120 python tools/bench_kernels.py 2048 ew 2>&1 | grep "softmax\|rmsnorm"
+PCV_CE_NOCACHE=1 PCV_KB_CUBLAS=0 timeout 120 python tools/bench_kernels.py 2048 ew 2>&1 | grep "softmax"
