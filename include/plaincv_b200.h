@@ -146,6 +146,32 @@ int pcv_adamw_step(float* p, const float* g, float* m, float* v, void* p_bf16, l
                    int n_partials, float* norm_out, double max_norm, double lr, double b1, double b2, double eps,
                    double weight_decay, int step, void* stream);
 
+/* ---- forward-mode (tangent) kernels for the GGN matvec of the LM ----
+ * The reference forms GGN.v = J^T H (J v) with jax.jvp / jax.vjp around Transformer.__call__
+ * (optim/ggn_utils.py:69-153, make_ggn_matvec_fn_lm).  J^T is the backward path above; J v needs the tangents below
+ * (a Dense tangent is two pcv_gemm_bf16 launches, RoPE is linear: pcv_rope_qk on the tangent).
+ *
+ * Tangent of residual add + nn.RMSNorm (transformer.py:41-47, 293, 334).  x[M][d] = the primal residual stream after
+ * the add, rstd[M] as saved by pcv_rmsnorm_residual_fwd; tres_out = bf16(tres_in + tdelta) (tdelta may be NULL: then
+ * tres_out is unused); ty = rstd*scale*(tx - xh*mean(xh*tx)) + xh*tscale with xh = x*rstd. */
+int pcv_rmsnorm_residual_jvp(const void* x, const float* rstd, const float* scale, const float* tscale,
+                             const void* tres_in, const void* tdelta, void* tres_out, void* ty, int M, int d,
+                             void* stream);
+/* th[M][hid] = silu'(g)*tg*u + silu(g)*tu for gu, tgu [M][2*hid] = [gate | up] (GLU, transformer.py:126). */
+int pcv_swiglu_jvp(const void* gu, const void* tgu, void* th, int M, int hid, void* stream);
+/* th = act'(x)*tx over n bf16 elements; mode as pcv_act_fwd (MLP / MLPReluSquared, transformer.py:70-97, 138-165). */
+int pcv_act_jvp(const void* x, const void* tx, void* th, long long n, int mode, void* stream);
+/* Tangent of jax.nn.dot_product_attention (transformer.py:233-240) on tcgen05/TMEM: qkv as for pcv_attn_fwd (rotated
+ * q, k), tqkv[B*T][3*d] its tangent (rotated likewise), out / lse the forward results; tout[B*T][d] =
+ * P.tV + (P*tS).V - rowsum(P*tS)*out with tS = (tQ.K^T + Q.tK^T)/sqrt(64); same causal / document masking. */
+int pcv_attn_jvp(const void* qkv, const void* tqkv, const int32_t* doc_start, const void* out, const float* lse,
+                 void* tout, int B, int T, int n_heads, void* stream);
+/* softmax_cross_entropy_hessian_vec (optim/ggn_utils.py:19-53) with the 1/(B*T) of :122-124 folded in:
+ * hv[M][ldl] = (p*v - p*(p.v)) * out_scale per row, p = softmax(fp32(logits[:, :V])); pad columns zero; bf16 in / out;
+ * hv may alias vec. */
+int pcv_ce_hessian_vec(const void* logits, const void* vec, void* hv, int M, int V, int ldl, float out_scale,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -61,6 +61,13 @@ SIGNATURES = {
     "pcv_sumsq_partials": (c_int, [c_void_p, c_longlong, c_void_p, c_int, c_void_p]),
     "pcv_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_void_p, c_int, c_void_p,
                                c_double, c_double, c_double, c_double, c_double, c_double, c_int, c_void_p]),
+    "pcv_rmsnorm_residual_jvp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_int, c_int, c_void_p]),
+    "pcv_swiglu_jvp": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "pcv_act_jvp": (c_int, [c_void_p, c_void_p, c_void_p, c_longlong, c_int, c_void_p]),
+    "pcv_attn_jvp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                             c_void_p]),
+    "pcv_ce_hessian_vec": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p]),
 }
 
 
