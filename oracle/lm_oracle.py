@@ -18,6 +18,7 @@ file restates their published semantics and follows the reference's own call sit
                              _clip_grads :173-178, _loss_and_acc :181-186, compute_grads :256-271
   data/datasets/data_prep_utils.py   intra_doc_causal_mask :14-43
   optim/factory.py           adamw branch :193-205 (optax.adamw, no mask -> decay on every leaf)
+  optim/ggn_utils.py         softmax_cross_entropy_hessian_vec :19-53, make_ggn_matvec_fn_lm :69-153
 
 Three numeric modes (`compute_dtype`):
   torch.float64  — for finite-difference gradient checks
@@ -385,6 +386,39 @@ def adamw_step(params: Params, grads: Params, m: Params, v: Params, step: int, l
 
 
 # ------------------------------------------------------------------------------------------------ synthetic data
+# ------------------------------------------------------------------------------------------------ GGN matvec (N4)
+def softmax_cross_entropy_hessian_vec(logits: torch.Tensor, labels: torch.Tensor, vec_logits: torch.Tensor):
+    """optim/ggn_utils.py:19-53: H = diag(p) - p p^T per row, applied to vec_logits; fp32 (fp64 stays fp64)."""
+    acc = torch.float64 if logits.dtype == torch.float64 else torch.float32
+    probs = torch.softmax(logits.to(acc), dim=-1)
+    v = vec_logits.to(acc)
+    return probs * v - probs * torch.sum(probs * v, dim=-1, keepdim=True)
+
+
+def ggn_matvec(params: Params, cfg: ModelConfig, vec: Params, input_ids: torch.Tensor, labels: torch.Tensor,
+               attn_mask: Optional[torch.Tensor] = None, compute_dtype: torch.dtype = torch.float32) -> Params:
+    """make_ggn_matvec_fn_lm, optim/ggn_utils.py:69-153: J^T H (J vec) / (B*T) with J = d logits / d params
+    (jax.jvp :110-114, Hessian-vec :116-127, jax.vjp :129-131); input_ids [n_probe, B, T] averages over probes
+    (:137-150)."""
+    from torch.func import jvp, vjp
+    if input_ids.dim() == 3:
+        outs = [ggn_matvec(params, cfg, vec, input_ids[i], labels[i], None if attn_mask is None else attn_mask[i],
+                           compute_dtype) for i in range(input_ids.shape[0])]
+        return {k: sum(o[k] for o in outs) / float(len(outs)) for k in outs[0]}
+
+    def logits_fn(p):
+        return forward(p, cfg, input_ids, attn_mask, compute_dtype)
+
+    vec = {k: vec[k] for k in params}  # same leaf order as the parameter tree
+    logits, jvp_logits = jvp(logits_fn, (params,), (vec,))
+    b, t, v = logits.shape
+    hv2 = softmax_cross_entropy_hessian_vec(logits.reshape(b * t, v), labels.reshape(b * t), jvp_logits.reshape(b * t, v))
+    hv_logits = (hv2.reshape(b, t, v) / float(b * t)).to(logits.dtype)
+    _, vjp_fun = vjp(logits_fn, params)
+    (hv_params,) = vjp_fun(hv_logits)
+    return hv_params
+
+
 def synthetic_batch(batch_size: int, seq_len: int, vocab_size: int, seed: int = 1234,
                     doc_mean: Optional[int] = None) -> dict:
     """The loader's batch contract (data/lm_loader.py:32-38): input_ids int [B, T+1] and, when doc_mean is given,

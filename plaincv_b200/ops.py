@@ -281,6 +281,70 @@ def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, V: int, grad_scale: f
     return out2, (logits if write_grad else None)
 
 
+# ------------------------------------------------------------------------------------------------ tangents (N4)
+def add_bf16(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    out = torch.empty_like(a) if out is None else out
+    check(_lib.load().pcv_add_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), a.numel(), _stream()), "pcv_add_bf16")
+    return out
+
+
+def linear_jvp(tx: torch.Tensor, w: torch.Tensor, x: torch.Tensor, tw: torch.Tensor) -> torch.Tensor:
+    """Tangent of y = x @ w: ty = tx @ w + x @ tw, each product rounded to bf16 like the primal Dense output
+    (jax.jvp of nn.Dense in the compute dtype), summed by pcv_add_bf16."""
+    a = linear_fwd(tx, w)
+    return add_bf16(a, linear_fwd(x, tw), a)
+
+
+def rmsnorm_residual_jvp(x: torch.Tensor, rstd: torch.Tensor, scale: torch.Tensor, tscale: torch.Tensor,
+                         tres_in: torch.Tensor, tdelta: Optional[torch.Tensor]):
+    """-> (tres_out, ty) for the primal (res_out = x, rstd) of rmsnorm_residual_fwd; tres_out is tres_in when
+    tdelta is None."""
+    M, d = x.shape
+    ty = torch.empty_like(x)
+    tres_out = torch.empty_like(x) if tdelta is not None else tres_in
+    check(_lib.load().pcv_rmsnorm_residual_jvp(x.data_ptr(), rstd.data_ptr(), scale.data_ptr(), tscale.data_ptr(),
+                                               tres_in.data_ptr(), _p(tdelta),
+                                               tres_out.data_ptr() if tdelta is not None else None, ty.data_ptr(),
+                                               M, d, _stream()), "pcv_rmsnorm_residual_jvp")
+    return tres_out, ty
+
+
+def swiglu_jvp(gu: torch.Tensor, tgu: torch.Tensor) -> torch.Tensor:
+    M, two_h = gu.shape
+    th = torch.empty((M, two_h // 2), dtype=torch.bfloat16, device=gu.device)
+    check(_lib.load().pcv_swiglu_jvp(gu.data_ptr(), tgu.data_ptr(), th.data_ptr(), M, two_h // 2, _stream()),
+          "pcv_swiglu_jvp")
+    return th
+
+
+def act_jvp(x: torch.Tensor, tx: torch.Tensor, mlp: str) -> torch.Tensor:
+    th = torch.empty_like(x)
+    check(_lib.load().pcv_act_jvp(x.data_ptr(), tx.data_ptr(), th.data_ptr(), x.numel(), _ACT_MODE[mlp], _stream()),
+          "pcv_act_jvp")
+    return th
+
+
+def attn_jvp(qkv: torch.Tensor, tqkv: torch.Tensor, doc_start: Optional[torch.Tensor], out: torch.Tensor,
+             lse: torch.Tensor, B: int, T: int, n_heads: int) -> torch.Tensor:
+    """Tangent of attn_fwd: qkv / tqkv rotated (q, k columns), out / lse from attn_fwd."""
+    tout = torch.empty_like(out)
+    check(_lib.load().pcv_attn_jvp(qkv.data_ptr(), tqkv.data_ptr(), _p(doc_start), out.data_ptr(), lse.data_ptr(),
+                                   tout.data_ptr(), B, T, n_heads, _stream()), "pcv_attn_jvp")
+    return tout
+
+
+def ce_hessian_vec(logits: torch.Tensor, vec: torch.Tensor, V: int, out_scale: float,
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(diag(p) - p p^T) vec * out_scale per row of bf16 logits[M, ldl] (optim/ggn_utils.py:19-53); `out` may be vec."""
+    _req(logits, torch.bfloat16, "ce_hessian_vec")
+    _req(vec, torch.bfloat16, "ce_hessian_vec")
+    M, ldl = logits.shape
+    out = torch.empty_like(vec) if out is None else out
+    check(_lib.load().pcv_ce_hessian_vec(logits.data_ptr(), vec.data_ptr(), out.data_ptr(), M, V, ldl, float(out_scale),
+                                         _stream()), "pcv_ce_hessian_vec")
+    return out
+
+
 def rope_table(head_dim: int, seq_len: int, theta: float, device) -> torch.Tensor:
     """cos/sin table [T][hd/2][2] fp32, computed exactly as precompute_freqs_cis (models/LM/embedding.py:8-26) does:
     a one-off host-side constant, uploaded once."""

@@ -274,3 +274,61 @@ def test_oracle_reproduces_golden(name):
         flat = g.reshape(-1)
         for i, val in zip(rec["index"], rec["values"]):
             assert abs(float(flat[i]) - val) <= 1e-4 * abs(val) + 1e-4 * rec["norm"] / math.sqrt(flat.numel()), (k, i)
+
+
+# ------------------------------------------------------------------------------------------------ GGN matvec (N4)
+def test_ce_hessian_vec_is_the_hessian_of_the_row_loss():
+    """optim/ggn_utils.py:19-53: H v with H = diag(p) - p p^T equals autograd's Hessian of -log softmax(z)[y]."""
+    g = torch.Generator().manual_seed(0)
+    z = torch.randn(3, 7, generator=g, dtype=torch.float64)
+    y = torch.tensor([1, 6, 3])
+    v = torch.randn(3, 7, generator=g, dtype=torch.float64)
+    hv = O.softmax_cross_entropy_hessian_vec(z, y, v)
+    for r in range(3):
+        H = torch.autograd.functional.hessian(lambda zz: torch.logsumexp(zz, -1) - zz[y[r]], z[r])
+        assert torch.allclose(hv[r], H @ v[r], atol=1e-12)
+    assert torch.allclose(hv.sum(-1), torch.zeros(3, dtype=torch.float64), atol=1e-12)  # 1^T H = 0
+
+
+@pytest.mark.parametrize("use_doc", [False, True])
+def test_ggn_matvec_equals_explicit_jt_h_j(use_doc):
+    """make_ggn_matvec_fn_lm (optim/ggn_utils.py:69-153) on a micro model in fp64: the jvp / vjp composition equals
+    J^T blockdiag(H_token) J v / (B*T) with J built explicitly by autograd; symmetric and positive semi-definite."""
+    cfg = O.ModelConfig(vocab_size=11, seq_len=6, dim=8, expand=8 / 3, n_layers=1, n_heads=2)
+    params = O.init_params(cfg, seed=3, dtype=torch.float64)
+    params = {k: v * 10 for k, v in params.items()}  # away from the near-linear regime of the 0.02 init
+    g = torch.Generator().manual_seed(4)
+    ids = torch.randint(0, 11, (2, 6), generator=g)
+    labels = torch.randint(0, 11, (2, 6), generator=g)
+    mask = None
+    if use_doc:
+        mask = torch.stack([O.intra_doc_causal_mask([2, 4], 6), O.intra_doc_causal_mask([3, 1, 2], 6)])
+    names = sorted(params)
+    sizes = [params[k].numel() for k in names]
+
+    def unflat(x):
+        out, o = {}, 0
+        for k, n in zip(names, sizes):
+            out[k] = x[o:o + n].view(params[k].shape)
+            o += n
+        return out
+
+    flat = torch.cat([params[k].reshape(-1) for k in names])
+    J = torch.autograd.functional.jacobian(
+        lambda x: O.forward(unflat(x), cfg, ids, mask, torch.float64).reshape(-1), flat)  # [B*T*V, P]
+    logits = O.forward(params, cfg, ids, mask, torch.float64).reshape(12, 11)
+    p = torch.softmax(logits, -1)
+    H = torch.block_diag(*[torch.diag(p[r]) - torch.outer(p[r], p[r]) for r in range(12)])
+    G = J.t() @ H @ J / 12.0
+    v = torch.randn(flat.numel(), generator=g, dtype=torch.float64)
+    gv = O.ggn_matvec(params, cfg, unflat(v), ids, labels, mask, torch.float64)
+    gv_flat = torch.cat([gv[k].reshape(-1) for k in names])
+    assert torch.allclose(gv_flat, G @ v, rtol=1e-8, atol=1e-10)
+    assert torch.allclose(G, G.t(), atol=1e-12) and float(v @ gv_flat) >= 0
+    # probe batches: the mean of the per-probe products (:137-150)
+    both = O.ggn_matvec(params, cfg, unflat(v), torch.stack([ids, ids.flip(0)]), torch.stack([labels, labels]),
+                        None if mask is None else torch.stack([mask, mask.flip(0)]), torch.float64)
+    other = O.ggn_matvec(params, cfg, unflat(v), ids.flip(0), labels, None if mask is None else mask.flip(0),
+                         torch.float64)
+    for k in names:
+        assert torch.allclose(both[k], 0.5 * (gv[k] + other[k]), atol=1e-12)
