@@ -90,12 +90,15 @@ rmsnorm_residual_jvp_kernel(const __nv_bfloat16* __restrict__ x, const float* __
   for (int i = 0; i < VPL; ++i) {
     const int v = lane + 32 * i;
     if (v < vpr) {
+      const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + v * 8));
+      const float4 s1 = __ldg(reinterpret_cast<const float4*>(scale + v * 8 + 4));
+      const float4 t0 = __ldg(reinterpret_cast<const float4*>(tscale + v * 8));
+      const float4 t1 = __ldg(reinterpret_cast<const float4*>(tscale + v * 8 + 4));
+      const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+      const float ts[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
       float o[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float s = __ldg(scale + v * 8 + j), ts = __ldg(tscale + v * 8 + j);
-        o[j] = rstd * s * (tx[i][j] - xh[i][j] * dot) + xh[i][j] * ts;
-      }
+      for (int j = 0; j < 8; ++j) o[j] = rstd * sc[j] * (tx[i][j] - xh[i][j] * dot) + xh[i][j] * ts[j];
       *reinterpret_cast<uint4*>(ty + base + v * 8) = pack8(o);
     }
   }
@@ -170,9 +173,12 @@ __device__ __forceinline__ float block_reduce(float v, float* sh, bool is_max) {
   return r;
 }
 
+// kCache: the logits row is staged in shared memory by the first pass, so the later passes re-read only `vec`.
+template <bool kCache>
 __global__ void __launch_bounds__(kHvThreads)
 ce_hessian_vec_kernel(const __nv_bfloat16* __restrict__ logits, const __nv_bfloat16* vec, __nv_bfloat16* hv, int V,
                       int ldl, float out_scale) {  // hv may be vec itself (each thread rewrites only what it read)
+  extern __shared__ uint4 hv_row_cache[];
   __shared__ float sh[kHvThreads / 32];
   const int tid = threadIdx.x;
   const long off = static_cast<long>(blockIdx.x) * ldl;
@@ -182,18 +188,20 @@ ce_hessian_vec_kernel(const __nv_bfloat16* __restrict__ logits, const __nv_bfloa
   const int nvec = ldl / 8;
   float m = -FLT_MAX;
   for (int v = tid; v < nvec; v += kHvThreads) {
+    const uint4 raw = __ldg(lrow + v);
+    if (kCache) hv_row_cache[v] = raw;
     float f[8];
-    unpack8(lrow[v], f);
+    unpack8(raw, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j)
       if (v * 8 + j < V) m = fmaxf(m, f[j]);
   }
-  m = block_reduce(m, sh, true);
+  m = block_reduce(m, sh, true);  // (its barriers also publish the row cache)
   const float mb = m * kLog2eC;
   float se = 0.f, sev = 0.f;
   for (int v = tid; v < nvec; v += kHvThreads) {
     float f[8], t[8];
-    unpack8(lrow[v], f);
+    unpack8(kCache ? hv_row_cache[v] : __ldg(lrow + v), f);
     unpack8(vrow[v], t);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -210,7 +218,7 @@ ce_hessian_vec_kernel(const __nv_bfloat16* __restrict__ logits, const __nv_bfloa
   const float inner = sev * inv;  // p^T v
   for (int v = tid; v < nvec; v += kHvThreads) {
     float f[8], t[8], o[8];
-    unpack8(lrow[v], f);
+    unpack8(kCache ? hv_row_cache[v] : __ldg(lrow + v), f);
     unpack8(vrow[v], t);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -228,17 +236,20 @@ ce_hessian_vec_kernel(const __nv_bfloat16* __restrict__ logits, const __nv_bfloa
 // so one flash-style pass accumulates tO' = P tV + W V (W = P * tS) in tensor memory and delta in a register; the
 // rank-one correction with the saved forward output O is applied when the tile is written.
 //
-// CTA (192 threads) = one (batch, head, 128-query tile):
-//   warps 0-3 : one thread per query row: S and tS from TMEM -> P, W (bf16 pairs) back into TMEM, delta
-//   warp 4    : TMA producer (Q, tQ once; K, tK, V, tV ring of 2 stages) + TMEM allocation
-//   warp 5    : tcgen05.mma issuer: S = Q.K^T; tS = tQ.K^T + Q.tK^T; tO' += P.tV + W.V (A operands from TMEM)
+// CTA (320 threads) = one (batch, head, 128-query tile):
+//   warps 0-7 : two warpgroups, each one thread per query row and half of the tile's 128 key columns: S and tS from
+//               TMEM -> P, W (bf16 pairs) back into TMEM, partial delta (exchanged through shared memory at the end);
+//               the epilogue splits the 64 output dims the same way
+//   warp 8    : TMA producer (Q, tQ once; K, tK, V, tV ring of 2 stages) + TMEM allocation
+//   warp 9    : tcgen05.mma issuer: S = Q.K^T; tS = tQ.K^T + Q.tK^T; tO' += P.tV + W.V (A operands from TMEM)
 // TMEM: S [0,128) tS [128,256) tO' [256,320) P [320,384) W [384,448).
-constexpr int kJvpThreads = 192;
+constexpr int kJvpThreads = 320;
 struct AttnJvpSmem {
   static constexpr int kQ = 0;                        // Q, tQ
   static constexpr int kRing = kQ + 2 * kTile;        // 2 stages x (K, tK, V, tV)
   static constexpr int kBar = kRing + 8 * kTile;
-  static constexpr int kBytes = kBar + 256 + 1024;
+  static constexpr int kDelta = kBar + 256;           // [2][128] fp32 partial deltas
+  static constexpr int kBytes = kDelta + 1024 + 1024; // + alignment slack
 };
 
 __global__ void __launch_bounds__(kJvpThreads, 1)
@@ -258,7 +269,7 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   auto bVfull = [&](int s) { return sBar + 8u * (3 + s); };   // [2] (tx)
   auto bEmpty = [&](int s) { return sBar + 8u * (5 + s); };   // [2] (1, commit)
   const uint32_t bSfull = sBar + 8u * 7;                      // (1, commit)
-  const uint32_t bPfull = sBar + 8u * 8;                      // (128)
+  const uint32_t bPfull = sBar + 8u * 8;                      // (256)
   const uint32_t bPVdone = sBar + 8u * 9;                     // (1, commit)
   const uint32_t tmem_ptr_smem = sBar + 8u * 10;
   volatile uint32_t* tmem_ptr_generic =
@@ -275,7 +286,7 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const int jlo = doc_start ? (doc_start[seq_row0 + q0] / 128) : 0;
   const int n_it = jhi - jlo + 1;
 
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_tqkv);
     mbar_init(bQ, 1);
@@ -285,11 +296,11 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_init(bEmpty(s), 1);
     }
     mbar_init(bSfull, 1);
-    mbar_init(bPfull, 128);
+    mbar_init(bPfull, 256);
     mbar_init(bPVdone, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == 8) {
     __syncwarp();
     tmem_alloc<512>(tmem_ptr_smem);
   }
@@ -298,7 +309,7 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
 
-  if (warp == 4) {
+  if (warp == 8) {
     // ============================== TMA producer ==============================
     if (lane == 0) {
       mbar_expect_tx(bQ, 2 * kTile);
@@ -317,7 +328,7 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
     }
     __syncwarp();
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ============================== MMA issuer ==============================
     const uint32_t lead = elect_one_sync();
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
@@ -369,10 +380,11 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     __syncwarp();
   } else {
     // ============================== softmax rows ==============================
-    const int r = tid;  // 0..127
+    const int wg = warp >> 2;   // key columns [64 wg, 64 wg + 64) of every tile, output dims [32 wg, 32 wg + 32)
+    const int r = tid & 127;
     const int t = q0 + r;
     const int ds_t = doc_start ? doc_start[seq_row0 + t] : 0;
-    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t tS = tmem_base + lane_off, tTS = tS + 128, tO = tS + 256, tP = tS + 320, tW = tS + 384;
     constexpr float c2 = kScaleC * kLog2eC;
     const float lse2 = lse[(static_cast<long>(b) * NH + h) * T + t] * kLog2eC;
@@ -383,7 +395,8 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tc_fence_after();
       const int lo0 = ds_t - key0, hi0 = t - key0;  // visible key window of this row, relative to the tile
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = 2 * wg + cc;
         uint32_t sr[32], tr[32];
         tmem_ld_32x32b_x32(tS + c * 32, sr);
         tmem_ld_32x32b_x32(tTS + c * 32, tr);
@@ -402,7 +415,7 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           pk[k >> 1] = pack_bf16x2(e0, e1);
           pw[k >> 1] = pack_bf16x2(w0, w1);
         }
-        if (c == 0 && idx > 0) {  // the previous tile's P.tV / W.V still read P and W until this fires
+        if (cc == 0 && idx > 0) {  // the previous tile's P.tV / W.V still read P and W until this fires
           mbar_wait(bPVdone, (idx - 1) & 1);
           tc_fence_after();
         }
@@ -413,31 +426,32 @@ attn_jvp_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tc_fence_before();
       mbar_arrive(bPfull);
     }
-    // ---- epilogue: tO = tO' - delta * O
+    // ---- the two halves of a row's delta meet in shared memory
+    float* sdelta = reinterpret_cast<float*>(smem_raw + (sbase + AttnJvpSmem::kDelta - smem_u32(smem_raw)));
+    sdelta[wg * 128 + r] = delta;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    delta += sdelta[(wg ^ 1) * 128 + r];
+    // ---- epilogue: tO = tO' - delta * O, this warpgroup's 32 of the 64 output dims
     mbar_wait(bPVdone, (n_it - 1) & 1);
     tc_fence_after();
-    uint32_t o0[32], o1[32];
-    tmem_ld_32x32b_x32(tO, o0);
-    tmem_ld_32x32b_x32(tO + 32, o1);
+    uint32_t o0[32];
+    tmem_ld_32x32b_x32(tO + 32 * wg, o0);
     tmem_ld_wait();
-    const long grow = (seq_row0 + t) * d + h * 64;
+    const long grow = (seq_row0 + t) * d + h * 64 + 32 * wg;
     const uint4* osrc = reinterpret_cast<const uint4*>(out + grow);
     uint4* odst = reinterpret_cast<uint4*>(tout + grow);
 #pragma unroll
-    for (int v = 0; v < 8; ++v) {
+    for (int v = 0; v < 4; ++v) {
       float of[8], res[8];
       unpack8(__ldg(osrc + v), of);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float acc = __uint_as_float(v < 4 ? o0[v * 8 + j] : o1[(v - 4) * 8 + j]);
-        res[j] = acc - delta * of[j];
-      }
+      for (int j = 0; j < 8; ++j) res[j] = __uint_as_float(o0[v * 8 + j]) - delta * of[j];
       odst[v] = pack8(res);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
@@ -472,7 +486,8 @@ extern "C" int pcv_rmsnorm_residual_jvp(const void* x, const float* rstd, const 
                                         void* stream) {
   if (!x || !rstd || !scale || !tscale || !tres_in || !ty || M <= 0 || d <= 0 || d > 2048) return PCV_ERR_ARG;
   if (tdelta && !tres_out) return PCV_ERR_ARG;
-  if (d % 8 || !al16(x) || !al16(tres_in) || !al16(ty) || (tdelta && !al16(tdelta)) || (tres_out && !al16(tres_out)))
+  if (d % 8 || !al16(x) || !al16(tres_in) || !al16(ty) || !al16(scale) || !al16(tscale) || (tdelta && !al16(tdelta)) ||
+      (tres_out && !al16(tres_out)))
     return PCV_ERR_ALIGN;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch ((d / 8 + 31) / 32) {
@@ -509,9 +524,24 @@ extern "C" int pcv_ce_hessian_vec(const void* logits, const void* vec, void* hv,
                                   void* stream) {
   if (!logits || !vec || !hv || M <= 0 || V <= 0 || V > ldl) return PCV_ERR_ARG;
   if (ldl % 8 || !al16(logits) || !al16(vec) || !al16(hv)) return PCV_ERR_ALIGN;
-  ce_hessian_vec_kernel<<<M, kHvThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(logits), static_cast<const __nv_bfloat16*>(vec), static_cast<__nv_bfloat16*>(hv),
-      V, ldl, out_scale);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t row_bytes = static_cast<size_t>(ldl) * 2;
+  if (row_bytes <= 110 * 1024) {  // two blocks per SM keep their rows in shared memory
+    auto kern = ce_hessian_vec_kernel<true>;
+    static bool attr = false;
+    if (!attr) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      attr = true;
+    }
+    kern<<<M, kHvThreads, row_bytes, st>>>(static_cast<const __nv_bfloat16*>(logits),
+                                           static_cast<const __nv_bfloat16*>(vec), static_cast<__nv_bfloat16*>(hv), V,
+                                           ldl, out_scale);
+  } else {
+    ce_hessian_vec_kernel<false><<<M, kHvThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(logits),
+                                                           static_cast<const __nv_bfloat16*>(vec),
+                                                           static_cast<__nv_bfloat16*>(hv), V, ldl, out_scale);
+  }
   count_launch();
   return cuda_rc();
 }

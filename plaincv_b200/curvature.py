@@ -40,14 +40,16 @@ def softmax_cross_entropy_hessian_vec(logits: torch.Tensor, labels: Optional[tor
 
 
 class _HeadCotangentFn(torch.autograd.Function):
-    """out_norm + lm_head whose backward takes the logits cotangent from `box["cot"]` (bf16 [M, V_pad]) instead of a
-    loss: the J^T leg of the GGN product.  Forward returns a dummy scalar to call .backward() on."""
+    """out_norm (+ the LM head in backward) whose backward takes the logits cotangent from `box["cot"]` (bf16
+    [M, V_pad]) instead of a loss: the J^T leg of the GGN product.  Forward leaves (res_f, rstd, hf) in `box["head"]`
+    for the tangent pass and returns a dummy scalar to call .backward() on."""
 
     @staticmethod
     def forward(ctx, res, delta, head, rt, box):
         res_f, hf, rstd = ops.rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
         ctx.save_for_backward(res_f, rstd, hf)
         ctx.head, ctx.has_delta, ctx.box = head, delta is not None, box
+        box["head"] = (res_f, rstd, hf)
         return torch.zeros((), dtype=torch.float32, device=res.device)
 
     @staticmethod
@@ -107,52 +109,73 @@ def _head_matmul(hf: torch.Tensor, w: torch.Tensor, head) -> torch.Tensor:
 
 
 @torch.no_grad()
+def _tangent_pass(model: Transformer, ids: torch.Tensor, rt, tape, head_state, tangent: TangentBuffers) -> torch.Tensor:
+    """J vec -> bf16 [B*T, V_pad] from the primal activations of one forward pass: `tape[i]` = what block i saved
+    for its backward (ops.BlockFn), `head_state` = (res_f, rstd, hf) of the final norm."""
+    L, nh, B, T = model.layout, model.cfg.n_heads, rt.B, rt.T
+    tf32, tb16 = tangent.f32, tangent.bf16
+    tres = ops.embed_fwd(ids, L.slot_view(tb16, "embed"), L.d)
+    tdelta = None
+    for i, layer in enumerate(model.layers):
+        p = f"layers_{i}"
+        res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh = tape[i]
+        tres1, th1 = ops.rmsnorm_residual_jvp(res1, rstd1, layer.attn_norm,
+                                              L.slot_view(tf32, f"{p}.attn_norm").view(-1), tres, tdelta)
+        tqkv = ops.linear_jvp(th1, layer.w_qkv, h1, L.slot_view(tb16, f"{p}.w_qkv"))
+        ops.rope_qk_(tqkv, rt.cos_sin, B, T, nh)  # RoPE is linear: the tangent rotates like the primal
+        to = ops.attn_jvp(qkv, tqkv, rt.doc_start, o, lse, B, T, nh)
+        ta = ops.linear_jvp(to, layer.w_out, o, L.slot_view(tb16, f"{p}.w_out"))
+        tres2, th2 = ops.rmsnorm_residual_jvp(res2, rstd2, layer.mlp_norm,
+                                              L.slot_view(tf32, f"{p}.mlp_norm").view(-1), tres1, ta)
+        tgu = ops.linear_jvp(th2, layer.w_gu, h2, L.slot_view(tb16, f"{p}.w_gu"))
+        thh = ops.swiglu_jvp(gu, tgu) if layer.mlp == "glu" else ops.act_jvp(gu, tgu, layer.mlp)
+        tdelta = ops.linear_jvp(thh, layer.w_down, hh, L.slot_view(tb16, f"{p}.w_down"))
+        tres = tres2
+    head = model.head
+    res_f, rstd, hf = head_state
+    _, thf = ops.rmsnorm_residual_jvp(res_f, rstd, head.out_norm, L.slot_view(tf32, "out_norm").view(-1), tres, tdelta)
+    t_head_w = L.slot_view(tb16, "embed" if head.tied else "w_lm")
+    a = _head_matmul(thf, head.w_lm, head)
+    return ops.add_bf16(a, _head_matmul(hf, t_head_w, head), a)
+
+
+@torch.no_grad()
 def jvp_logits(model: Transformer, input_ids: torch.Tensor, tangent: TangentBuffers, *,
                doc_start: Optional[torch.Tensor] = None, doc_lengths=None,
                attn_mask: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """jax.jvp(logits_fn, (params,), (vec,)) of optim/ggn_utils.py:110-114 -> (logits, J vec), both bf16
-    [B*T, V_pad] (pad columns zero).  Primal and tangent run side by side, layer by layer."""
+    [B*T, V_pad] (pad columns zero)."""
     ids, B, T, doc_start = model._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
     rt = model._runtime(B, T, doc_start)
-    L, eps, nh = model.layout, model.cfg.rmsnorm_eps, model.cfg.n_heads
-    tf32, tb16 = tangent.f32, tangent.bf16
-    t_embed = L.slot_view(tb16, "embed")
-    res = ops.embed_fwd(ids, model.embed_bf16, L.d)
-    tres = ops.embed_fwd(ids, t_embed, L.d)
-    delta = tdelta = None
-    for i, layer in enumerate(model.layers):
-        p = f"layers_{i}"
-        res1, h1, rstd1 = ops.rmsnorm_residual_fwd(res, delta, layer.attn_norm, eps)
-        tres1, th1 = ops.rmsnorm_residual_jvp(res1, rstd1, layer.attn_norm,
-                                              L.slot_view(tf32, f"{p}.attn_norm").view(-1), tres, tdelta)
-        qkv = ops.linear_fwd_rope(h1, layer.w_qkv, rt.cos_sin, T, 2 * nh * 64)
-        tqkv = ops.linear_jvp(th1, layer.w_qkv, h1, L.slot_view(tb16, f"{p}.w_qkv"))
-        ops.rope_qk_(tqkv, rt.cos_sin, B, T, nh)  # RoPE is linear: the tangent rotates like the primal
-        o, lse = ops.attn_fwd(qkv, doc_start, B, T, nh)
-        to = ops.attn_jvp(qkv, tqkv, doc_start, o, lse, B, T, nh)
-        a = ops.linear_fwd(o, layer.w_out)
-        ta = ops.linear_jvp(to, layer.w_out, o, L.slot_view(tb16, f"{p}.w_out"))
-        res2, h2, rstd2 = ops.rmsnorm_residual_fwd(res1, a, layer.mlp_norm, eps)
-        tres2, th2 = ops.rmsnorm_residual_jvp(res2, rstd2, layer.mlp_norm,
-                                              L.slot_view(tf32, f"{p}.mlp_norm").view(-1), tres1, ta)
-        t_gu_w = L.slot_view(tb16, f"{p}.w_gu")
-        if layer.mlp == "glu":
-            gu, hh = ops.linear_fwd_swiglu(h2, layer.w_gu)
-            thh = ops.swiglu_jvp(gu, ops.linear_jvp(th2, layer.w_gu, h2, t_gu_w))
-        else:
-            gu = ops.linear_fwd(h2, layer.w_gu)
-            hh = ops.act_fwd(gu, layer.mlp)
-            thh = ops.act_jvp(gu, ops.linear_jvp(th2, layer.w_gu, h2, t_gu_w), layer.mlp)
-        m = ops.linear_fwd(hh, layer.w_down)
-        tm = ops.linear_jvp(thh, layer.w_down, hh, L.slot_view(tb16, f"{p}.w_down"))
-        res, delta, tres, tdelta = res2, m, tres2, tm
+    rt.tape = []
+    res, delta = model._trunk(ids, rt)
     head = model.head
-    res_f, hf, rstd = ops.rmsnorm_residual_fwd(res, delta, head.out_norm, eps)
-    _, thf = ops.rmsnorm_residual_jvp(res_f, rstd, head.out_norm, L.slot_view(tf32, "out_norm").view(-1), tres, tdelta)
-    t_head_w = L.slot_view(tb16, "embed" if head.tied else "w_lm")
+    res_f, hf, rstd = ops.rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
     logits = _head_matmul(hf, head.w_lm, head)
-    tlogits = ops.add_bf16(_head_matmul(thf, head.w_lm, head), _head_matmul(hf, t_head_w, head))
-    return logits, tlogits
+    return logits, _tangent_pass(model, ids, rt, rt.tape, (res_f, rstd, hf), tangent)
+
+
+def ggn_product_accumulate(model: Transformer, input_ids: torch.Tensor, tangent: TangentBuffers, out_scale: float, *,
+                           doc_start: Optional[torch.Tensor] = None, doc_lengths=None,
+                           attn_mask: Optional[torch.Tensor] = None) -> None:
+    """model.flat_grad += out_scale * J^T H J vec for one batch (optim/ggn_utils.py:94-131): ONE primal forward feeds
+    both the tangent pass (jax.jvp, :110-114) and the transpose (jax.vjp, :129-131) — the blocks leave their saved
+    activations on a tape; the Hessian-vector product (:116-127) overwrites J vec in place."""
+    ids, B, T, doc_start = model._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
+    rt = model._runtime(B, T, doc_start)
+    rt.tape = []
+    box: dict = {}
+    with torch.enable_grad():
+        res, delta = model._trunk(ids, rt)
+        dummy = _HeadCotangentFn.apply(res, delta, model.head, rt, box)
+    with torch.no_grad():
+        head_state = box.pop("head")
+        tlogits = _tangent_pass(model, ids, rt, rt.tape, head_state, tangent)
+        rt.tape = None
+        logits = _head_matmul(head_state[2], model.head.w_lm, model.head)
+        box["cot"] = ops.ce_hessian_vec(logits, tlogits, model.cfg.vocab_size, out_scale, out=tlogits)
+        del logits, tlogits, head_state
+    dummy.backward()
 
 
 def vjp_logits_accumulate(model: Transformer, input_ids: torch.Tensor, cotangent: torch.Tensor, *,
@@ -207,13 +230,8 @@ def make_ggn_matvec_fn_lm(model_def: Transformer, curvature_batch: Sequence, bat
         model.flat_grad.zero_()
         n_probe = len(probes)
         for ids_b, mk in zip(probes, masks):
-            kw = _mask_kwargs(mk)
-            logits, tlogits = jvp_logits(model, ids_b, tangent, **kw)
-            M = logits.shape[0]
-            # H (J vec) / (B*T), cast to the logits dtype (:116-127); the mean over probe batches (:149-150) rides along
-            hv = ops.ce_hessian_vec(logits, tlogits, model.cfg.vocab_size, 1.0 / (M * n_probe), out=tlogits)
-            del logits
-            vjp_logits_accumulate(model, ids_b, hv, **kw)
+            # H (J vec) / (B*T) (:116-127); the mean over probe batches (:149-150) rides along in the same scale
+            ggn_product_accumulate(model, ids_b, tangent, 1.0 / (ids_b.numel() * n_probe), **_mask_kwargs(mk))
         return model.export_flax_grads()
 
     return ggn_matvec

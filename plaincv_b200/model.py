@@ -224,7 +224,7 @@ class _HeadHandles:
 class _Runtime:
     """Per-call constants shared by every block of one forward pass."""
 
-    __slots__ = ("eps", "cos_sin", "doc_start", "B", "T", "n_heads")
+    __slots__ = ("eps", "cos_sin", "doc_start", "B", "T", "n_heads", "tape")
 
 
 # ------------------------------------------------------------------------------------------------ the module
@@ -359,6 +359,7 @@ class Transformer(nn.Module):
         rt = _Runtime()
         rt.eps, rt.cos_sin, rt.doc_start = self.cfg.rmsnorm_eps, self.cos_sin, doc_start
         rt.B, rt.T, rt.n_heads = B, T, self.cfg.n_heads
+        rt.tape = None  # a list: every block appends its saved activations (read by the tangent pass, curvature.py)
         return rt
 
     def _prep_inputs(self, input_ids, attn_mask, doc_lengths, doc_start):

@@ -521,6 +521,8 @@ class BlockFn(torch.autograd.Function):
             hh = act_fwd(gu, layer.mlp)
         m = linear_fwd(hh, layer.w_down)
         ctx.save_for_backward(res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh)
+        if rt.tape is not None:
+            rt.tape.append((res1, rstd1, h1, qkv, o, lse, res2, rstd2, h2, gu, hh))
         ctx.layer, ctx.rt, ctx.has_delta = layer, rt, delta is not None
         return res2, m
 
