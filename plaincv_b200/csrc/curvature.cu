@@ -61,17 +61,28 @@ rmsnorm_residual_jvp_kernel(const __nv_bfloat16* __restrict__ x, const float* __
   const int vpr = d / 8;
   const long base = static_cast<long>(row) * d;
   const float rstd = rstd_in[row];
+  // every load of the row is issued before the first use
+  uint4 rx[VPL], rt[VPL], rd[VPL];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int v = lane + 32 * i;
+    if (v < vpr) {
+      rx[i] = *reinterpret_cast<const uint4*>(x + base + v * 8);
+      rt[i] = *reinterpret_cast<const uint4*>(tres_in + base + v * 8);
+      if (tdelta != nullptr) rd[i] = *reinterpret_cast<const uint4*>(tdelta + base + v * 8);
+    }
+  }
   float xh[VPL][8], tx[VPL][8];
   float dot = 0.f;
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
     const int v = lane + 32 * i;
     if (v < vpr) {
-      unpack8(*reinterpret_cast<const uint4*>(x + base + v * 8), xh[i]);
-      unpack8(*reinterpret_cast<const uint4*>(tres_in + base + v * 8), tx[i]);
+      unpack8(rx[i], xh[i]);
+      unpack8(rt[i], tx[i]);
       if (tdelta != nullptr) {
         float t[8];
-        unpack8(*reinterpret_cast<const uint4*>(tdelta + base + v * 8), t);
+        unpack8(rd[i], t);
 #pragma unroll
         for (int j = 0; j < 8; ++j) tx[i][j] += t[j];
         const uint4 r = pack8(tx[i]);

@@ -93,20 +93,27 @@ rmsnorm_residual_fwd_kernel(const __nv_bfloat16* __restrict__ res_in, const __nv
   if (row >= M) return;
   const int vpr = d / 8;
   const long base = static_cast<long>(row) * d;
+  // every load of the row is in flight before the first use (the interleaved form left the second vector's loads
+  // behind the first vector's store: 58 -> 37 us on the tangent twin of this kernel)
+  bf16x8 ra[VPL], rb[VPL];
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int v = lane + 32 * i;
+    if (v < vpr) {
+      ra[i].raw = *reinterpret_cast<const uint4*>(res_in + base + v * 8);
+      if (delta != nullptr) rb[i].raw = *reinterpret_cast<const uint4*>(delta + base + v * 8);
+    }
+  }
   float x[VPL][8];
   float ss = 0.f;
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
     const int v = lane + 32 * i;
     if (v < vpr) {
-      bf16x8 a;
-      a.raw = *reinterpret_cast<const uint4*>(res_in + base + v * 8);
-      a.unpack(x[i]);
+      ra[i].unpack(x[i]);
       if (delta != nullptr) {
-        bf16x8 b;
-        b.raw = *reinterpret_cast<const uint4*>(delta + base + v * 8);
         float t[8];
-        b.unpack(t);
+        rb[i].unpack(t);
 #pragma unroll
         for (int j = 0; j < 8; ++j) x[i][j] += t[j];
         // the residual stream is bf16 in the reference (x = x + f(...) in the compute dtype): round, then norm

@@ -533,7 +533,11 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         const int n0 = (EPI == EPI_SWIGLU) ? wk.n_blk * 128 + static_cast<int>(rank) * p.half_off
                        : wk.narrow         ? wk.n_blk * BN + wk.ncol0 + static_cast<int>(rank) * 64
                                            : wk.n_blk * BN + static_cast<int>(rank) * 128;
-        const uint32_t tx = wk.narrow ? 2 * (Cfg::kABytes + Cfg::kBBytes / 2) : 2 * Cfg::kStageBytes;
+        uint32_t tx = wk.narrow ? 2 * (Cfg::kABytes + Cfg::kBBytes / 2) : 2 * Cfg::kStageBytes;
+        // measurement only: leave out the B (64) / A (128) operand loads to see how much of the mainloop is the L2 -> SM feed
+        const bool skip_b = (p.dbg & 64) != 0, skip_a = (p.dbg & 128) != 0 && !skip_b;  // never both: nothing would arm the barrier
+        if (skip_b) tx -= wk.narrow ? Cfg::kBBytes : 2 * Cfg::kBBytes;
+        if (skip_a) tx -= 2 * Cfg::kABytes;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           if (rank == 0) mbar_expect_tx(full_bar(stage), tx);
@@ -541,13 +545,15 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           const uint32_t sa = smem_a + stage * Cfg::kABytes;
           const uint32_t sb = smem_b + stage * Cfg::kBBytes;
           const int k0 = kb * kBK;
-          if constexpr (!A_MN) {
+          if (skip_a) {  // (with both skipped the leader's arrive.expect_tx of 0 bytes completes the phase by itself)
+          } else if constexpr (!A_MN) {
             tma_load_2d_pair(sa, &tma_a, bar, k0, m0);
           } else {
 #pragma unroll
             for (int i = 0; i < 2; ++i) tma_load_2d_pair(sa + i * (64 * kBK * 2), &tma_a, bar, m0 + 64 * i, k0);
           }
-          if constexpr (!B_MN) {
+          if (skip_b) {
+          } else if constexpr (!B_MN) {
             if (wk.narrow) tma_load_2d_pair(sb, &tma_bn, bar, k0, n0);
             else tma_load_2d_pair(sb, &tma_b, bar, k0, n0);
           } else {
@@ -1075,7 +1081,7 @@ extern "C" int pcv_gemm_set_profile(void* dev_buf) {
 }
 
 extern "C" int pcv_gemm_set_mode(int mode) {
-  if (mode >= 100 && mode < 164) { pcv::g_gemm_dbg = mode - 100; return PCV_OK; }
+  if (mode >= 100 && mode < 356) { pcv::g_gemm_dbg = mode - 100; return PCV_OK; }
   if (mode < 0 || mode > 4) return PCV_ERR_ARG;
   if (mode >= 3) pcv::g_gemm_tail = mode == 4;
   else pcv::g_gemm_mode = mode;

@@ -252,3 +252,34 @@ def test_ggn_properties_full_size_c3_shapes():
     g2v = matvec(None, {k: 2.0 * w for k, w in v.items()})
     for k in ("layers_0/attn/w_qkv/kernel", "layers_1/mlp/fc2/kernel", "lm_head/kernel", "embed_tokens/embedding"):
         assert rel_l2(g2v[k], 2.0 * gv[k]) < 2e-2, k
+
+
+def test_ggn_matvec_against_golden_fixture():
+    """The CUDA GGN matvec against tests/golden/small_ragged.json (oracle fp32 output committed by
+    tools/make_golden.py: ragged vocab 1003, packed documents), without running the oracle: v^T G v within 2e-2,
+    per-leaf norms within 3e-2, sampled entries within 8e-2 relative + 1.5e-1 of the leaf's rms."""
+    import json
+    import os
+    from plaincv_b200.batch import prepare_batch, synthetic_batch
+    from plaincv_b200.curvature import make_ggn_matvec_fn_lm
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "small_ragged.json")) as f:
+        gold = json.load(f)
+    spec = gold["spec"]
+    cfg_o = O.ModelConfig(vocab_size=spec["vocab_size"], seq_len=spec["seq_len"], dim=spec["dim"], expand=8 / 3,
+                          n_layers=spec["n_layers"], n_heads=spec["n_heads"])
+    model, params = _build(cfg_o, seed=spec["seed"])
+    batch = synthetic_batch(spec["batch"], spec["seq_len"], spec["vocab_size"], seed=spec["data_seed"],
+                            doc_mean=spec["doc_mean"])
+    inputs, labels, doc_start = prepare_batch(batch, spec["seq_len"], True)
+    g = torch.Generator().manual_seed(gold["ggn"]["seed"])
+    vec = {k: torch.randn(v.shape, generator=g) * (0.02 if v.dim() > 1 else 0.1) for k, v in params.items()}
+    gv = make_ggn_matvec_fn_lm(model, (inputs, labels, doc_start))(None, vec)   # document starts instead of a mask
+    vGv = _dot(vec, gv)
+    assert abs(vGv - gold["ggn"]["vGv"]) <= 2e-2 * gold["ggn"]["vGv"], (vGv, gold["ggn"]["vGv"])
+    for k, rec in gold["ggn"]["leaves"].items():
+        got = gv[k].float().cpu()
+        assert abs(float(got.double().norm()) - rec["norm"]) <= 3e-2 * rec["norm"], (k, float(got.norm()), rec["norm"])
+        rms = rec["norm"] / math.sqrt(got.numel())
+        flat = got.reshape(-1)
+        for i, val in zip(rec["index"], rec["values"]):
+            assert abs(float(flat[i]) - val) <= 8e-2 * abs(val) + 1.5e-1 * rms, (k, i, float(flat[i]), val)

@@ -274,6 +274,14 @@ def test_oracle_reproduces_golden(name):
         flat = g.reshape(-1)
         for i, val in zip(rec["index"], rec["values"]):
             assert abs(float(flat[i]) - val) <= 1e-4 * abs(val) + 1e-4 * rec["norm"] / math.sqrt(flat.numel()), (k, i)
+    if "ggn" in gold:  # the GGN matvec fixture along the seeded direction of tools/make_golden.py
+        g = torch.Generator().manual_seed(gold["ggn"]["seed"])
+        vec = {k: torch.randn(v.shape, generator=g) * (0.02 if v.dim() > 1 else 0.1) for k, v in params.items()}
+        gv = O.ggn_matvec(params, cfg, vec, inputs, labels, mask, torch.float32)
+        vGv = float(sum((vec[k].double() * gv[k].double()).sum() for k in gv))
+        assert abs(vGv - gold["ggn"]["vGv"]) <= 1e-4 * gold["ggn"]["vGv"]
+        for k, rec in gold["ggn"]["leaves"].items():
+            assert abs(float(gv[k].double().norm()) - rec["norm"]) <= 1e-3 * rec["norm"] + 1e-12, k
 
 
 # ------------------------------------------------------------------------------------------------ GGN matvec (N4)

@@ -28,7 +28,7 @@ CASES = {
                        data_seed=77),
     # a 2-layer, 2-head model with a small ragged vocab: cheap enough for every CPU run
     "small_ragged": dict(vocab_size=1003, seq_len=128, dim=128, n_layers=2, n_heads=2, batch=3, doc_mean=40, seed=2,
-                         data_seed=5),
+                         data_seed=5, ggn_seed=17),
 }
 
 
@@ -42,6 +42,12 @@ def hash_name(name: str) -> int:
     for ch in name.encode():
         h = ((h ^ ch) * 16777619) & 0xFFFFFFFF
     return h
+
+
+def ggn_direction(params, seed: int):
+    """The seeded parameter-shaped direction of the GGN fixtures (kernels N(0, 0.02), norm scales N(0, 0.1))."""
+    g = torch.Generator().manual_seed(seed)
+    return {k: torch.randn(v.shape, generator=g) * (0.02 if v.dim() > 1 else 0.1) for k, v in params.items()}
 
 
 def run_case(spec: dict) -> dict:
@@ -60,7 +66,19 @@ def run_case(spec: dict) -> dict:
         idx = sample_index(k, flat.numel())
         leaves[k] = {"shape": list(g.shape), "norm": float(g.double().norm()), "index": idx,
                      "values": [float(flat[i]) for i in idx]}
-    return {"spec": spec, "loss": float(loss), "acc": float(acc), "n_params": O.count_params(params),
+    extra = {}
+    if spec.get("ggn_seed") is not None:
+        # GGN matvec (optim/ggn_utils.py:69-153) along a seeded direction: per-leaf norms, sampled entries
+        vec = ggn_direction(params, spec["ggn_seed"])
+        gv = O.ggn_matvec(params, cfg, vec, inputs, labels, mask, torch.float32)
+        rec = {}
+        for k, g in gv.items():
+            flat = g.reshape(-1)
+            idx = sample_index(k, flat.numel())
+            rec[k] = {"norm": float(g.double().norm()), "index": idx, "values": [float(flat[i]) for i in idx]}
+        extra["ggn"] = {"seed": spec["ggn_seed"], "vGv": float(sum((vec[k].double() * gv[k].double()).sum() for k in gv)),
+                        "leaves": rec}
+    return {"spec": spec, "loss": float(loss), "acc": float(acc), "n_params": O.count_params(params), **extra,
             "input_ids_sum": int(np.asarray(batch["input_ids"]).astype(np.int64).sum()),
             "docs_lengths": batch.get("docs_lengths"), "grads": leaves}
 
