@@ -124,7 +124,8 @@ def _attn_ref(q, k, v, doc_start):
     return torch.einsum("bnts,bsnh->btnh", torch.softmax(s, -1), v)
 
 
-@pytest.mark.parametrize("B,T,NH,doc_mean", [(2, 128, 2, None), (1, 384, 3, None), (2, 512, 2, 100), (1, 1024, 1, 300)])
+@pytest.mark.parametrize("B,T,NH,doc_mean", [(2, 128, 2, None), (1, 384, 3, None), (2, 512, 2, 100), (1, 1024, 1, 300),
+                                             (1, 2048, 2, 512), (1, 4096, 1, None)])
 def test_attention_jvp(ops, B, T, NH, doc_mean):
     """pcv_attn_jvp against torch.func.jvp of fp32 softmax attention on the same bf16-rounded q, k, v and tangents."""
     g = torch.Generator().manual_seed(T + NH)

@@ -164,7 +164,10 @@ def _doc_starts(B, T, seed, mean):
 
 
 @pytest.mark.parametrize("B,T,NH,doc_mean", [(2, 256, 4, None), (1, 1024, 2, None), (2, 512, 3, 150), (1, 1024, 2, 40),
-                                             (1, 128, 1, None), (2, 384, 2, 1000)])
+                                             (1, 128, 1, None), (2, 384, 2, 1000),
+                                             # BASELINE's full sequence lengths: C3 / C5 (2048, packed documents of
+                                             # mean 512) and C4 (4096), one or two heads so the fp32 oracle stays cheap
+                                             (1, 2048, 2, None), (1, 2048, 2, 512), (1, 4096, 1, None), (1, 4096, 1, 700)])
 def test_attention_fwd_bwd(ops, B, T, NH, doc_mean):
     g = torch.Generator().manual_seed(5)
     d = NH * 64
