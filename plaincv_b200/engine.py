@@ -10,6 +10,8 @@ One process per GPU (torchrun).  Differences from the reference that are deliber
 """
 from __future__ import annotations
 
+import os
+
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -115,19 +117,43 @@ class GradReducer:
             self._handles = []
 
 
+def bucket_groups(n_layers: int, layers_per_bucket: int) -> List[Tuple[int, int]]:
+    """(lowest, highest) layer index of every gradient bucket, in the order backward completes them (top layers
+    first).  Groups hold up to `layers_per_bucket` layers and taper — never more than half of the layers still ahead —
+    down to single layers for the last two, so that little is left to reduce once backward has ended."""
+    G = max(1, int(layers_per_bucket))
+    groups = []
+    hi = n_layers - 1
+    while hi >= 0:
+        size = min(G, max(1, (hi + 1) // 2))
+        lo = hi - size + 1
+        groups.append((lo, hi))
+        hi = lo - 1
+    return groups
+
+
 class Engine:
     """compute_grads / eval_step / train_step over a plaincv_b200.Transformer."""
 
     def __init__(self, model, seq_len: Optional[int] = None, use_doc_mask: bool = False, process_group=None,
-                 overlap: bool = True, grad_comm_dtype: torch.dtype = torch.bfloat16):
+                 overlap: bool = True, grad_comm_dtype: torch.dtype = torch.bfloat16,
+                 layers_per_bucket: Optional[int] = None):
         self.model = model
         self.seq_len = int(seq_len if seq_len is not None else model.cfg.seq_len)
         self.use_doc_mask = bool(use_doc_mask)
         self.overlap = overlap
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         L = model.layout
-        # buckets in the order their gradients become final during backward: head, layers L-1..0, embedding
-        self._ranges = [L.head_range] + list(reversed(L.layer_ranges)) + [L.embed_range]
+        # buckets in the order their gradients become final during backward: head, layers L-1..0 (consecutive layers
+        # are contiguous in the flat buffer, so `layers_per_bucket` of them form one slice), embedding
+        # Fewer, larger all-reduces cost less (26 -> 8 collectives at 24 layers: -0.85 ms per step on 2 GPUs), but what
+        # the last bucket holds is reduced after backward has ended — so the groups taper: up to `layers_per_bucket`
+        # (default 8) layers while much of backward is still ahead, halving towards single layers at the end.
+        if layers_per_bucket is None:
+            layers_per_bucket = int(os.environ.get("PCV_DDP_LAYERS_PER_BUCKET", "8"))
+        self._groups = bucket_groups(len(L.layer_ranges), layers_per_bucket)
+        self._ranges = ([L.head_range] + [(L.layer_ranges[lo][0], L.layer_ranges[hi][1]) for lo, hi in self._groups]
+                        + [L.embed_range])
         self.reducer = GradReducer(model.flat_grad, self._ranges, process_group, comm_dtype=grad_comm_dtype)
 
     # ------------------------------------------------------------------ hooks
@@ -135,9 +161,10 @@ class Engine:
         m = self.model
         if on and self.world > 1 and self.overlap:
             m.head.on_grads_ready = lambda: self.reducer.bucket_ready(0)
-            n = len(m.layers)
-            for i, layer in enumerate(m.layers):
-                layer.on_grads_ready = (lambda k=(1 + (n - 1 - i)): self.reducer.bucket_ready(k))
+            for layer in m.layers:
+                layer.on_grads_ready = None
+            for g, (lo, _hi) in enumerate(self._groups):  # a group is complete when its lowest layer's backward is
+                m.layers[lo].on_grads_ready = (lambda k=1 + g: self.reducer.bucket_ready(k))
         else:
             m.head.on_grads_ready = None
             for layer in m.layers:

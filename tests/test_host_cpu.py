@@ -120,6 +120,21 @@ def test_param_layout_mirrors_flax_tree():
                                    mlp_class="glu", seq_len=8, dtype="int8"))
 
 
+def test_bucket_groups_partition_the_layers_in_backward_order():
+    """Engine's gradient buckets: contiguous layer groups, top layers first, every layer exactly once, at most
+    `layers_per_bucket` per group, tapering to single layers at the end of backward."""
+    from plaincv_b200.engine import bucket_groups
+    assert bucket_groups(24, 8) == [(16, 23), (8, 15), (4, 7), (2, 3), (1, 1), (0, 0)]
+    assert bucket_groups(24, 1) == [(i, i) for i in range(23, -1, -1)]
+    for n in (1, 2, 3, 4, 12, 24, 25):
+        for g in (1, 2, 4, 8, 100):
+            groups = bucket_groups(n, g)
+            covered = [i for lo, hi in groups for i in range(hi, lo - 1, -1)]
+            assert covered == list(range(n - 1, -1, -1)), (n, g, groups)
+            assert all(hi - lo + 1 <= g for lo, hi in groups)
+            assert groups[-1] == (0, 0)
+
+
 def test_product_path_refuses_cpu():
     from plaincv_b200.model import ModelConfig, Transformer
     cfg = ModelConfig(vocab_size=64, seq_len=64, dim=64, expand=8 / 3, n_layers=1, n_heads=1)
