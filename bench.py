@@ -287,10 +287,11 @@ def gpu_main(args) -> None:
     ds_d = None if ds_h is None else ds_h.to(dev)
 
     def step_resident():
-        model.flat_grad.zero_()
         model.sync_compute_weights()
+        eng.zero_grads_async()  # in stream order by default (a side-stream zero-fill under the forward pass measured 1 % slower)
         eng._arm_hooks(True)
         loss, acc = model.loss_and_acc(inputs_d, labels_d, doc_start=ds_d, unit_grad=True)
+        eng.wait_zero_grads()
         loss.backward()
         if world > 1:
             eng.reducer.finish()

@@ -155,6 +155,8 @@ class Engine:
         self._ranges = ([L.head_range] + [(L.layer_ranges[lo][0], L.layer_ranges[hi][1]) for lo, hi in self._groups]
                         + [L.embed_range])
         self.reducer = GradReducer(model.flat_grad, self._ranges, process_group, comm_dtype=grad_comm_dtype)
+        self._zero_stream = None
+        self._zero_pending = False
 
     # ------------------------------------------------------------------ hooks
     def _arm_hooks(self, on: bool) -> None:
@@ -189,13 +191,36 @@ class Engine:
 
         return up(inputs), up(labels), up(doc_start)
 
+    def zero_grads_async(self) -> None:
+        """Zero the flat gradient buffer.  PCV_ZERO_ASYNC=1 moves the 1.6 GB memset (0.25 ms at C3) to a side stream
+        so that it runs under the forward pass (nothing touches the buffer before backward) — measured on B200 this
+        LOSES 1 % (47.9 vs 47.4 ms per step: the memset takes HBM / L2 bandwidth from the forward GEMMs for longer than
+        it would have run alone), so the default zeroes in stream order."""
+        g = self.model.flat_grad
+        if not g.is_cuda or os.environ.get("PCV_ZERO_ASYNC", "0") != "1":
+            g.zero_()
+            return
+        if self._zero_stream is None:
+            self._zero_stream = torch.cuda.Stream(device=g.device)
+        self._zero_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._zero_stream):
+            g.zero_()
+        self._zero_pending = True
+
+    def wait_zero_grads(self) -> None:
+        """Backward (the first writer of the gradient buffer) must not start before the zero-fill has finished."""
+        if self._zero_pending:
+            torch.cuda.current_stream().wait_stream(self._zero_stream)
+            self._zero_pending = False
+
     def _micro(self, batch: dict, accumulate: bool, sync: bool, loss_scale: float, stat: torch.Tensor) -> None:
         m = self.model
         inputs, labels, doc_start = self._to_device(batch)
         if not accumulate:
-            m.flat_grad.zero_()
+            self.zero_grads_async()
         self._arm_hooks(sync)
         loss, acc = m.loss_and_acc(inputs, labels, doc_start=doc_start, loss_scale=loss_scale, unit_grad=True)
+        self.wait_zero_grads()
         loss.backward()
         stat[0] += loss.detach()
         stat[1] += acc.detach()
