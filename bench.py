@@ -11,8 +11,9 @@ uniform tokens, random-init weights.  One "step" = zero grads, bf16 weight refre
 bucketed gradient all-reduce.  Prints ONE JSON line on rank 0.
 
 `value`  : tokens/s with the token ids already resident in HBM (CUDA events, max over ranks).
-`e2e`    : the same through Engine.compute_grads(batch) with HOST (pinned) token ids, H2D copy and a D2H read of the
-           loss inside the timed region every step.
+`e2e`    : the same through the public API with HOST rows: BatchFeeder (collate + _prepare_batch on a worker thread,
+           pinned ring, H2D on a copy stream) -> Engine.compute_grads, H2D copies and a D2H read of the loss inside the
+           timed region every step.
 `roofline`: the dominant kernel (the tcgen05 GEMM): model GEMM FLOPs of one step / the CUDA-event time of exactly that
            GEMM sequence replayed back to back, against MEASURED_PEAKS.json's sustained bf16 figure.
 `cpu_baseline` / `--impl reference`: the reference's JAX path cannot run here (jax is not installed); the timed CPU
@@ -328,14 +329,22 @@ def gpu_main(args) -> None:
 
     ms_step, launches, clocks, _ = timed(step_resident, args.steps, args.warmup)
 
-    # end to end: host batch -> Engine.compute_grads -> loss read back, every step
+    # end to end through the public API: host rows -> BatchFeeder (collate + _prepare_batch on a worker thread, pinned
+    # ring, H2D on a copy stream) -> Engine.compute_grads -> loss read back, every step
+    from plaincv_b200.feed import BatchFeeder, InMemoryTokenDataset
+    host_rows = InMemoryTokenDataset.synthetic(4 * B, T, V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
+    feeder = BatchFeeder(host_rows, B, T, use_doc_mask=c["doc"], device=dev, depth=3)
+
     def step_e2e():
         model.sync_compute_weights()
-        loss, acc = eng.compute_grads(batch)
+        item = next(feeder)
+        loss, acc = eng.compute_grads(item)
+        feeder.release(item)
         return float(loss)  # device -> host read of the step's result
 
     ms_e2e, _, _, _ = timed(step_e2e, args.steps, min(args.warmup, 2) if args.warmup else 0)
     loss_val = step_e2e()
+    feeder.close()
 
     line = None
     if rank == 0:

@@ -131,6 +131,47 @@ class ArrowTokenDataset:
 
 
 # ------------------------------------------------------------------------------------------------ index streams
+class InMemoryTokenDataset:
+    """Rows held in host memory behind the same interface as ArrowTokenDataset (`len`, `[i]`, `rows(idx)`): the
+    synthetic-data mode the reference's README lists as a TODO.  `input_ids` int [n, T+1]; `docs_lengths` optional
+    list (one list of document lengths per row, each summing to T+1 — lm_loader.py:32-38)."""
+
+    def __init__(self, input_ids, docs_lengths: Optional[Sequence[Sequence[int]]] = None):
+        self._ids2d = np.ascontiguousarray(np.asarray(input_ids))
+        if self._ids2d.ndim != 2:
+            raise ValueError("input_ids must be [n_rows, seq_len + 1]")
+        if docs_lengths is not None and len(docs_lengths) != len(self._ids2d):
+            raise ValueError("docs_lengths must have one entry per row")
+        self._docs = None if docs_lengths is None else [list(map(int, d)) for d in docs_lengths]
+
+    @classmethod
+    def synthetic(cls, n_rows: int, seq_len: int, vocab_size: int, seed: int = 1234,
+                  doc_mean: Optional[int] = None) -> "InMemoryTokenDataset":
+        from .batch import synthetic_batch
+        b = synthetic_batch(n_rows, seq_len, vocab_size, seed=seed, doc_mean=doc_mean)
+        return cls(b["input_ids"], b.get("docs_lengths"))
+
+    def __len__(self) -> int:
+        return len(self._ids2d)
+
+    def __getitem__(self, i: int) -> Dict[str, object]:
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        out: Dict[str, object] = {"input_ids": self._ids2d[i]}
+        if self._docs is not None:
+            out["docs_lengths"] = list(self._docs[i])
+        return out
+
+    def rows(self, idx: Sequence[int]) -> Dict[str, object]:
+        j = np.asarray(idx, dtype=np.int64)
+        out: Dict[str, object] = {"input_ids": self._ids2d[j]}
+        if self._docs is not None:
+            out["docs_lengths"] = [list(self._docs[int(k)]) for k in j]
+        return out
+
+
 def epoch_indices(n: int, sampler: str = "sequential", *, batch_size: int = 1, seed: Optional[int] = None,
                   start_idx: int = 0, rng: Optional[np.random.Generator] = None) -> np.ndarray:
     """One epoch's row order for the samplers `_get_sampler_jax` offers (lm_loader.py:88-118):

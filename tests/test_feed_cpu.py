@@ -140,3 +140,29 @@ def test_feeder_resumes_and_shuffles_like_the_stateful_sampler():
         f.close()
     with pytest.raises(ValueError):
         feed.BatchFeeder(ds, 64, T)
+
+
+def test_in_memory_dataset_feeds_like_the_arrow_one():
+    """InMemoryTokenDataset (synthetic-data mode): same row / collate contract as ArrowTokenDataset, and BatchFeeder
+    over it yields exactly prepare_batch of consecutive row blocks, wrapping around at the end (drop_last)."""
+    import torch
+    from plaincv_b200.batch import prepare_batch
+    from plaincv_b200.feed import BatchFeeder, InMemoryTokenDataset
+    ds = InMemoryTokenDataset.synthetic(7, 64, 100, seed=3, doc_mean=20)
+    assert len(ds) == 7 and ds[0]["input_ids"].shape == (65,) and sum(ds[-1]["docs_lengths"]) == 65
+    r = ds.rows([4, 1])
+    assert r["input_ids"].shape == (2, 65) and r["docs_lengths"] == [ds[4]["docs_lengths"], ds[1]["docs_lengths"]]
+    with pytest.raises(IndexError):
+        ds[7]
+    with pytest.raises(ValueError):
+        InMemoryTokenDataset(np.zeros((3, 65), dtype=np.int32), docs_lengths=[[65]])
+    f = BatchFeeder(ds, 2, 64, use_doc_mask=True, device=None, depth=2)
+    try:
+        for blk in ([0, 1], [2, 3], [4, 5], [0, 1]):  # 7 rows, batches of 2: row 6 is dropped, then the stream wraps
+            item = next(f)
+            ref = prepare_batch(ds.rows(blk), 64, True)
+            assert torch.equal(item.inputs, ref[0]) and torch.equal(item.labels, ref[1])
+            assert torch.equal(item.doc_start, ref[2])
+            f.release(item)
+    finally:
+        f.close()
