@@ -85,7 +85,8 @@ def test_act_jvp(ops, mlp):
     assert rel_l2(th, ref) < 1e-2
 
 
-@pytest.mark.parametrize("M,V,ldl", [(16, 1000, 1024), (5, 50257, 50304), (7, 50280, 50304)])
+@pytest.mark.parametrize("M,V,ldl", [(16, 1000, 1024), (5, 50257, 50304), (7, 50280, 50304),
+                                     (3, 60001, 60032)])  # the last: a row too long for the shared-memory cache
 def test_ce_hessian_vec(ops, M, V, ldl):
     """pcv_ce_hessian_vec against softmax_cross_entropy_hessian_vec (optim/ggn_utils.py:19-53) as restated by the
     oracle; pad columns must come out zero; in-place form identical."""
