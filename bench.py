@@ -73,11 +73,14 @@ def gemm_flops_per_token(c: dict) -> float:
 def load_gemm_traffic(cname: str):
     """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one step's GEMM launches, from the committed
     `ncu --set full` capture summarised by tools/gemm_traffic.py (C3 shapes only); None when there is no capture."""
-    p = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
-    if cname != "c3" or not os.path.exists(p):
+    if cname != "c3":
         return None
-    with open(p) as f:
-        return json.load(f).get("step_bytes")
+    for name in ("r02_gemm_traffic.json", "r01_gemm_traffic.json"):
+        p = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(p):
+            with open(p) as f:
+                return json.load(f).get("step_bytes")
+    return None
 
 
 def load_peaks() -> dict:
@@ -252,52 +255,115 @@ def gemm_replay_ms(model, M: int, iters: int = 3) -> float:
     return e0.elapsed_time(e1) / iters
 
 
-def gpu_main(args) -> None:
+def attn_flops_per_token(c: dict, docs_lengths=None) -> float:
+    """Attention term of BASELINE.md §3.  Plain causal: 6*L*T*d per token.  Document-masked: every document of length n
+    attends n^2/2 pairs instead of T^2/2, so the term becomes 6*L*d*sum(n_i^2)/T, averaged over the batch's rows (the
+    lengths of the inputs, i.e. after train_lm.py:_trim_last_token)."""
+    d, L, T = c["d_model"], c["n_layers"], c["seq_len"]
+    if docs_lengths is None:
+        return 6.0 * L * T * d
+    from plaincv_b200.batch import trim_last_token
+    sq = [sum(n * n for n in trim_last_token(row)) for row in docs_lengths]
+    return 6.0 * L * d * (sum(sq) / len(sq)) / T
+
+
+_KERNEL_CLASSES = (("gemm_bf16", "gemm"), ("attn_fwd", "attn_fwd"), ("attn_bwd", "attn_bwd"), ("rmsnorm", "rmsnorm"),
+                   ("softmax_ce", "loss"), ("head_ce", "loss"), ("mean2", "loss"), ("nccl", "nccl"), ("cast", "cast"),
+                   ("embed", "embed"), ("swiglu", "swiglu"), ("Memset", "memset"), ("Memcpy", "memcpy"))
+
+
+def profile_one_step(fn) -> dict:
+    """Per-kernel durations INSIDE one real step (CUPTI through torch.profiler; the step's own streams, L2 state and
+    side-stream overlap — unlike the replay).  Durations of kernels that overlap on different streams are summed per
+    class, `busy_ms` is the union of all kernel intervals and `idle_ms` what is left of the step's span."""
     import torch
-    import torch.distributed as dist
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device; plaincv_b200 has no CPU fallback "
-                           "(use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    from plaincv_b200 import _lib
-    from plaincv_b200.engine import Engine
-    from plaincv_b200.model import construct_model
-    from plaincv_b200.batch import synthetic_batch
+    from torch.profiler import ProfilerActivity, profile
+    try:
+        fn()
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        iv, by = [], {}
+        for e in prof.events():
+            if e.device_type != torch.autograd.DeviceType.CUDA:
+                continue
+            t0, t1 = e.time_range.start, e.time_range.end
+            iv.append((t0, t1))
+            cls = "other"
+            for key, name in _KERNEL_CLASSES:
+                if key in e.name:
+                    cls = name
+                    break
+            rec = by.setdefault(cls, {"n": 0, "ms": 0.0})
+            rec["n"] += 1
+            rec["ms"] += (t1 - t0) / 1e3
+        if not iv:
+            return {"error": "profiler returned no device events"}
+        iv.sort()
+        busy, cur0, cur1 = 0.0, iv[0][0], iv[0][1]
+        for a, b in iv[1:]:
+            if a > cur1:
+                busy += cur1 - cur0
+                cur0, cur1 = a, b
+            else:
+                cur1 = max(cur1, b)
+        busy += cur1 - cur0
+        span = max(b for _, b in iv) - iv[0][0]
+        return {"span_ms": span / 1e3, "busy_ms": busy / 1e3, "idle_ms": (span - busy) / 1e3,
+                "by_kernel": {k: {"n": v["n"], "ms": round(v["ms"], 4)} for k, v in sorted(by.items())}}
+    except Exception as ex:  # the profiler is evidence, not the product: never fail the bench on it
+        return {"error": f"{type(ex).__name__}: {ex}"}
 
-    c = CONFIGS[args.config]
-    B, T, V = c["micro_batch"], c["seq_len"], c["vocab_size"]
-    model, mcfg = construct_model(yaml_like_cfg(c), device=dev)
-    # PCV_DDP_OVERLAP=0 (A/B runs only): all-reduce the buckets after backward instead of under it
-    # PCV_DDP_COMM=fp32 (A/B runs only): all-reduce the gradient buckets in fp32 instead of bf16
-    comm_fp32 = os.environ.get("PCV_DDP_COMM", "bf16") == "fp32"
-    eng = Engine(model, seq_len=T, use_doc_mask=c["doc"], overlap=os.environ.get("PCV_DDP_OVERLAP", "1") != "0",
-                 grad_comm_dtype=torch.float32 if comm_fp32 else torch.bfloat16)
-    lib = _lib.load()
-    tokens_per_step = B * T * world
 
-    batch = synthetic_batch(B, T, V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
-    inputs_h, labels_h, ds_h = eng_prepare(eng, batch)
-    inputs_d, labels_d = inputs_h.to(dev), labels_h.to(dev)
-    ds_d = None if ds_h is None else ds_h.to(dev)
+class Workload:
+    """One BASELINE config on this rank's GPU: model, engine, resident inputs and the timed step functions."""
 
-    def step_resident():
+    def __init__(self, cname: str, dev, rank: int, world: int):
+        import torch
+        from plaincv_b200.batch import synthetic_batch
+        from plaincv_b200.engine import Engine
+        from plaincv_b200.model import construct_model
+        self.cname, self.dev, self.rank, self.world = cname, dev, rank, world
+        c = self.c = CONFIGS[cname]
+        self.B, self.T, self.V = c["micro_batch"], c["seq_len"], c["vocab_size"]
+        self.model, _ = construct_model(yaml_like_cfg(c), device=dev)
+        # PCV_DDP_OVERLAP=0 (A/B runs only): all-reduce the buckets after backward instead of under it
+        # PCV_DDP_COMM=fp32 (A/B runs only): all-reduce the gradient buckets in fp32 instead of bf16
+        self.comm_fp32 = os.environ.get("PCV_DDP_COMM", "bf16") == "fp32"
+        self.eng = Engine(self.model, seq_len=self.T, use_doc_mask=c["doc"],
+                          overlap=os.environ.get("PCV_DDP_OVERLAP", "1") != "0",
+                          grad_comm_dtype=torch.float32 if self.comm_fp32 else torch.bfloat16)
+        self.batch = synthetic_batch(self.B, self.T, self.V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
+        inputs_h, labels_h, ds_h = eng_prepare(self.eng, self.batch)
+        self.inputs_d, self.labels_d = inputs_h.to(dev), labels_h.to(dev)
+        self.ds_d = None if ds_h is None else ds_h.to(dev)
+        self.tokens_per_step = self.B * self.T * world
+        self.fpt_causal = flops_per_token(c)
+        self.fpt = gemm_flops_per_token(c) + attn_flops_per_token(c, self.batch.get("docs_lengths"))
+
+    def step_resident(self):
+        model, eng = self.model, self.eng
         model.sync_compute_weights()
-        eng.zero_grads_async()  # in stream order by default (a side-stream zero-fill under the forward pass measured 1 % slower)
+        eng.zero_grads_async()  # in stream order by default (a side-stream zero-fill under the forward measured 1 % slower)
         eng._arm_hooks(True)
-        loss, acc = model.loss_and_acc(inputs_d, labels_d, doc_start=ds_d, unit_grad=True)
+        loss, acc = model.loss_and_acc(self.inputs_d, self.labels_d, doc_start=self.ds_d, unit_grad=True)
         eng.wait_zero_grads()
         loss.backward()
-        if world > 1:
+        if self.world > 1:
             eng.reducer.finish()
         eng._arm_hooks(False)
         return loss
+
+    def close(self):
+        import torch
+        self.model = self.eng = self.inputs_d = self.labels_d = self.ds_d = None
+        torch.cuda.empty_cache()
+
+
+def make_timer(dev, local_rank: int, world: int, lib):
+    import torch
+    import torch.distributed as dist
 
     def barrier():
         torch.cuda.synchronize()
@@ -313,27 +379,77 @@ def gpu_main(args) -> None:
         sampler.start()
         l0 = lib.pcv_launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0 = time.perf_counter()
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         barrier()
-        wall = time.perf_counter() - t0
         launches = lib.pcv_launch_count() - l0
         clocks = sampler.stop()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms) / steps, launches, clocks, wall
+        return float(ms) / steps, launches, clocks
 
-    ms_step, launches, clocks, _ = timed(step_resident, args.steps, args.warmup)
+    return timed
+
+
+def extra_config_line(cname: str, dev, rank, world, timed, peaks, min_seconds: float = 1.5) -> dict:
+    """The other BASELINE configs (C2, C4, C5) at the same N, each timed after the headline: tokens/s, ms/step, MFU,
+    clocks.  Enough steps for >= 3 clock samples (the 16 ms configs need ~100)."""
+    w = Workload(cname, dev, rank, world)
+    ms_probe, _, _ = timed(w.step_resident, 3, 3)
+    steps = max(10, int(min_seconds * 1e3 / ms_probe) + 1)
+    ms, launches, clocks = timed(w.step_resident, steps, 1)
+    tok_s = w.tokens_per_step / (ms / 1e3)
+    rec = {"workload": WORKLOAD_NAMES[cname], "value": tok_s, "unit": "tokens/s", "ms_per_step": ms, "steps": steps,
+           "warmup": 7, "micro_batch_per_gpu": w.B, "seq_len": w.T, "n_gpus": world,
+           "flop_per_token": w.fpt, "gpu_launches": int(launches), "clocks": clocks,
+           "mfu": {"of_burst_peak": tok_s * w.fpt / (world * peaks["bf16_tflops"] * 1e12),
+                   "of_sustained_peak": tok_s * w.fpt / (world * peaks["bf16_tflops_sustained"] * 1e12)}}
+    if w.c["doc"]:
+        rec["flop_per_token_plain_causal"] = w.fpt_causal
+        rec["mfu"]["of_burst_peak_if_counted_as_plain_causal"] = tok_s * w.fpt_causal / (world * peaks["bf16_tflops"] * 1e12)
+        rec["flops_note"] = "attention flops counted from this rank's actual documents: 6*L*d*sum(len^2)/T per token"
+    w.close()
+    return rec
+
+
+def gpu_main(args) -> None:
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus != world:
+        raise SystemExit(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}: launch N > 1 with "
+                         "`python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N`")
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device; plaincv_b200 has no CPU fallback "
+                           "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from plaincv_b200 import _lib
+    from plaincv_b200.batch import synthetic_batch
+
+    lib = _lib.load()
+    timed = make_timer(dev, local_rank, world, lib)
+    w = Workload(args.config, dev, rank, world)
+    c, B, T, V = w.c, w.B, w.T, w.V
+    model, eng = w.model, w.eng
+    comm_fp32 = w.comm_fp32
+    tokens_per_step = w.tokens_per_step
+
+    ms_step, launches, clocks = timed(w.step_resident, args.steps, args.warmup)
 
     # end to end through the public API: host rows -> BatchFeeder (collate + _prepare_batch on a worker thread, pinned
     # ring, H2D on a copy stream) -> Engine.compute_grads -> loss read back, every step
     from plaincv_b200.feed import BatchFeeder, InMemoryTokenDataset
     host_rows = InMemoryTokenDataset.synthetic(4 * B, T, V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
-    feeder = BatchFeeder(host_rows, B, T, use_doc_mask=c["doc"], device=dev, depth=3)
+    feeder = BatchFeeder(host_rows, B, T, use_doc_mask=c["doc"], device=dev, depth=3, vocab_size=V)
 
     def step_e2e():
         model.sync_compute_weights()
@@ -342,18 +458,45 @@ def gpu_main(args) -> None:
         feeder.release(item)
         return float(loss)  # device -> host read of the step's result
 
-    ms_e2e, _, _, _ = timed(step_e2e, args.steps, min(args.warmup, 2) if args.warmup else 0)
+    ms_e2e, _, _ = timed(step_e2e, args.steps, min(args.warmup, 2) if args.warmup else 0)
     loss_val = step_e2e()
     feeder.close()
 
+    # the reference's real schedule (config/tr_420M_x8gpu.yaml:35 grad_accumulation_steps: 4, train_lm.py:644-666): one
+    # optimizer step = 4 micro-batches; here the all-reduce runs once, under the last micro-batch's backward
+    micro = [{"input_ids": w.batch["input_ids"], **({"docs_lengths": w.batch["docs_lengths"]} if c["doc"] else {})}] * 4
+    micro_dev = [SimpleBatch(w.inputs_d, w.labels_d, w.ds_d)] * 4
+
+    def step_accum4():
+        model.sync_compute_weights()
+        return eng.train_step(micro_dev)
+
+    del micro
+    ms_acc4, _, _ = timed(step_accum4, max(2, args.steps // 4), 1)
+
+    in_step = profile_one_step(w.step_resident)
+
+    ddp = None
+    if world > 1 and not args.no_ddp_check:
+        from plaincv_b200.selfcheck import ddp_gradient_check
+        batches = [synthetic_batch(B, T, V, seed=1234 + k, doc_mean=512 if c["doc"] else None) for k in range(world)]
+        ddp = ddp_gradient_check(model, T, c["doc"], batches, rank, world)
+
     line = None
+    peaks = load_peaks()
     if rank == 0:
-        peaks = load_peaks()
-        fpt = flops_per_token(c)
+        fpt = w.fpt
         tok_s = tokens_per_step / (ms_step / 1e3)
         tok_s_e2e = tokens_per_step / (ms_e2e / 1e3)
         gemm_ms = gemm_replay_ms(model, B * T)
-        gemm_tf = gemm_flops_per_token(c) * B * T / (gemm_ms / 1e3) / 1e12
+        gemm_flop = gemm_flops_per_token(c) * B * T
+        gemm_tf = gemm_flop / (gemm_ms / 1e3) / 1e12
+        if "by_kernel" in in_step and "gemm" in in_step["by_kernel"]:
+            g_ms = in_step["by_kernel"]["gemm"]["ms"]
+            in_step["gemm_tflops"] = gemm_flop / (g_ms / 1e3) / 1e12
+            in_step["gemm_frac_of_sustained_peak"] = in_step["gemm_tflops"] / peaks["bf16_tflops_sustained"]
+            in_step["note"] = ("kernel durations inside one real step (CUPTI); wgrad GEMMs run on a side stream and "
+                               "overlap dgrad GEMMs, so class sums can exceed busy_ms")
         line = {
             "metric": "train tokens/s fwd+bwd", "value": tok_s, "unit": "tokens/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -371,16 +514,35 @@ def gpu_main(args) -> None:
                                                                                        (B * T * 4 if c["doc"] else 0)),
                     "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e},
             "gpu_launches": int(launches), "clocks": clocks, "loss": loss_val,
-            "roofline": {"kernel": "pcv::gemm_bf16_kernel (all Dense fwd/dgrad/wgrad launches of one step)",
+            "roofline": {"kernel": "pcv::gemm_bf16_pair_kernel (all Dense fwd/dgrad/wgrad launches of one step)",
                          "bound": "tensor", "achieved": gemm_tf, "peak": peaks["bf16_tflops_sustained"] / 1.0,
                          "unit": "TFLOP/s", "frac": gemm_tf / peaks["bf16_tflops_sustained"],
+                         "frac_of_burst_peak": gemm_tf / peaks["bf16_tflops"],
                          "traffic": load_gemm_traffic(args.config),
-                         "traffic_note": "DRAM bytes of the same launches (one step), ncu --set full, "
-                                         "profiles/r01_gemm_traffic.json; algorithmic flops per step = "
-                                         f"{gemm_flops_per_token(c) * B * T:.4g}",
+                         "traffic_note": "DRAM bytes of the same launches (one step), ncu --set full; "
+                                         f"algorithmic flops per step = {gemm_flop:.4g}",
                          "peak_source": peaks["_source"] + " bf16_tflops_sustained",
-                         "gemm_ms_per_step": gemm_ms, "gemm_share_of_step": gemm_ms / ms_step},
+                         "gemm_ms_per_step": gemm_ms, "gemm_share_of_step": gemm_ms / ms_step,
+                         "in_step": in_step},
+            "accum4": {"value": 4 * tokens_per_step / (ms_acc4 / 1e3), "unit": "tokens/s",
+                       "ms_per_optimizer_step": ms_acc4,
+                       "note": "the reference's schedule (grad_accumulation_steps: 4): 4 micro-batches per optimizer "
+                               "step, one gradient all-reduce under the last backward"},
         }
+        if ddp is not None:
+            line["ddp_check"] = ddp
+    w.close()
+    del model, eng
+
+    extras = {}
+    if not args.no_extra_configs and args.config == "c3":
+        for cname in ("c2", "c4", "c5"):
+            rec = extra_config_line(cname, dev, rank, world, timed, peaks)
+            if rank == 0:
+                extras[cname] = rec
+    if rank == 0:
+        if extras:
+            line["configs"] = extras
         if world == 1 and not args.no_cpu_baseline:
             cb = run_cpu_arm(args.config, 2, 1, max_seconds=90.0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -388,6 +550,13 @@ def gpu_main(args) -> None:
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+class SimpleBatch:
+    """A prepared, device-resident micro-batch in the shape Engine accepts from feed.BatchFeeder."""
+
+    def __init__(self, inputs, labels, doc_start):
+        self.inputs, self.labels, self.doc_start = inputs, labels, doc_start
 
 
 def eng_prepare(eng, batch):
@@ -404,6 +573,8 @@ def main() -> None:
     ap.add_argument("--config", default="c3", choices=sorted(CONFIGS))
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-configs", action="store_true", help="skip the C2 / C4 / C5 lines appended under 'configs'")
+    ap.add_argument("--no-ddp-check", action="store_true", help="skip the N-rank gradient check run after the timed region")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_main(args)

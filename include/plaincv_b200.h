@@ -6,7 +6,10 @@
  * functions:
  *   - take raw device pointers, sizes and a cudaStream_t (as void*); they never allocate and never synchronise;
  *   - return 0 on success, a positive cudaError_t, or one of the negative PCV_ERR_* codes below;
- *   - are re-entrant (the only global state is a mutex-guarded cache of TMA descriptors).
+ *   - are re-entrant: the only global state is a mutex-guarded cache of TMA descriptors, two launch counters and the
+ *     tiling override of pcv_gemm_set_mode (relaxed atomics; every setting computes the same product).
+ *     Measurement-only switches (epilogue cycle counters, leaving out operand loads / stores) exist only in
+ *     -DPCV_MEASURE builds of the library and are not part of this ABI.
  * Activations are bf16 row-major [tokens, features]; master parameters and gradients are fp32.
  */
 #ifndef PLAINCV_B200_H_
@@ -44,10 +47,8 @@ int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
 /* Tiling override for tests and benchmarks: 0 = automatic (CTA-pair 256x256 tiles, tcgen05 cta_group::2, whenever they
  * fill the machine; single-CTA 128xBN tiles otherwise), 1 = single-CTA tiles only, 2 = CTA-pair tiles always. */
 int pcv_gemm_set_mode(int mode);
-/* Measurement hook: when dev_buf is non-null the epilogue warps of the CTA-pair GEMMs write, per (CTA, epilogue warp),
- * 8 uint32: cycles waiting for the accumulator, waiting for epilogue operands, in the math, in the stores, total.
- * dev_buf holds grid x 8 x 8 uint32 (grid <= number of SMs); null switches it off. */
-int pcv_gemm_set_profile(void* dev_buf);
+/* Number of CTA-pair (tcgen05 cta_group::2) GEMM launches since load: lets a test assert which tiling ran. */
+long long pcv_gemm_pair_launch_count(void);
 
 /* fp32 master -> bf16 compute copy, zero-filling the padded tail columns: dst[rows][dst_ld] <- src[rows][src_ld][:cols].
  * Replaces flax's per-call promote_dtype of `kernel`/`embedding` (transformer.py: every nn.Dense / nn.Embed). */

@@ -31,7 +31,7 @@ SIGNATURES = {
     "pcv_gemm_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                               c_int, c_int, c_float, c_void_p]),
     "pcv_gemm_set_mode": (c_int, [c_int]),
-    "pcv_gemm_set_profile": (c_int, [c_void_p]),
+    "pcv_gemm_pair_launch_count": (c_longlong, []),
     "pcv_cast_pad_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "pcv_embed_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pcv_embed_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
@@ -98,8 +98,11 @@ def load() -> ctypes.CDLL:
         lib.pcv_gemm_set_mode(int(os.environ["PCV_GEMM_MODE"]))
     if "PCV_GEMM_TAIL" in os.environ:
         lib.pcv_gemm_set_mode(4 if os.environ["PCV_GEMM_TAIL"] != "0" else 3)
+    # PCV_GEMM_DBG (leave out operand loads / epilogue stores) exists only in a -DPCV_MEASURE build of the library
+    # (make XFLAGS=-DPCV_MEASURE); the shipped library rejects it, so a stray variable cannot corrupt results
     if "PCV_GEMM_DBG" in os.environ:
-        lib.pcv_gemm_set_mode(100 + int(os.environ["PCV_GEMM_DBG"]))
+        if lib.pcv_gemm_set_mode(100 + int(os.environ["PCV_GEMM_DBG"])) != 0:
+            raise RuntimeError("PCV_GEMM_DBG needs a measurement build of libplaincv_b200.so (make XFLAGS=-DPCV_MEASURE)")
     _lib = lib
     return lib
 

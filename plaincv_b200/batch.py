@@ -66,12 +66,27 @@ def dense_mask_from_doc_start(doc_start: np.ndarray) -> np.ndarray:
     return (s[None, None, :] >= ds[:, :, None]) & (s[None, None, :] <= s[None, :, None])
 
 
-def prepare_batch(batch: dict, seq_len: int, use_doc_mask: bool) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
-    """train_lm.py:134-148 -> (inputs int32 [B,T], labels int32 [B,T], doc_start int32 [B,T] | None), host tensors."""
+def check_token_range(input_ids: torch.Tensor, vocab_size: int) -> None:
+    """The kernels use token ids as raw row indices (embedding gather, its scatter-add transpose, the label pick of
+    the loss) — an id outside [0, vocab_size), e.g. data tokenised with another vocabulary, would read or red.add
+    outside the table.  XLA clamps gathers silently; here the batch is rejected on the host (one min/max pass)."""
+    if input_ids.numel() == 0:
+        return
+    lo, hi = int(input_ids.min()), int(input_ids.max())
+    if lo < 0 or hi >= vocab_size:
+        raise ValueError(f"token ids must lie in [0, {vocab_size}); batch holds [{lo}, {hi}]")
+
+
+def prepare_batch(batch: dict, seq_len: int, use_doc_mask: bool,
+                  vocab_size: Optional[int] = None) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
+    """train_lm.py:134-148 -> (inputs int32 [B,T], labels int32 [B,T], doc_start int32 [B,T] | None), host tensors.
+    vocab_size (optional): reject token ids outside [0, vocab_size) (check_token_range)."""
     input_ids = torch.as_tensor(np.asarray(batch["input_ids"])).to(torch.int32)
     if input_ids.dim() != 2 or input_ids.shape[1] != seq_len + 1:
         got = input_ids.shape[1] if input_ids.dim() == 2 else tuple(input_ids.shape)
         raise ValueError(f"Expected input_ids length {seq_len + 1} (seq_len+1) but got {got}.")
+    if vocab_size is not None:
+        check_token_range(input_ids, vocab_size)
     inputs = input_ids[:, :-1]
     labels = input_ids[:, 1:]
     doc_start = None

@@ -22,6 +22,7 @@
 #include "sm100.cuh"
 #include "pcv_internal.h"
 
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 
@@ -59,9 +60,20 @@ struct GemmParams {
   // CTA-pair kernel, tail of the persistent schedule: the tiles of the last, partial wave (index >= full_tiles) are cut
   // into two 256 x 128 halves when that lets every pair work on it (narrow = 1), instead of leaving pairs idle
   int full_tiles, narrow;
-  unsigned int* prof;  // measurement only (pcv_gemm_set_profile): per epilogue warp, cycles spent per phase
-  int dbg;  // measurement only (pcv_gemm_set_mode(100 + flags)): leave out parts of the fused epilogues
+#ifdef PCV_MEASURE
+  // -DPCV_MEASURE builds only (never the shipped library): per-phase cycle counters of the epilogue warps
+  // (pcv_gemm_set_profile) and switches that leave out operand loads / epilogue stores (pcv_gemm_set_mode(100 + flags))
+  unsigned int* prof;
+  int dbg;
+#endif
 };
+#ifdef PCV_MEASURE
+#define PCV_DBG(p, bits) (((p).dbg & (bits)) != 0)
+#define PCV_PROF(p) ((p).prof != nullptr)
+#else
+#define PCV_DBG(p, bits) false
+#define PCV_PROF(p) false
+#endif
 constexpr int EPI_BF16_ROPE = 3;  // internal: PCV_EPI_BF16 + RoPE (pcv_gemm_bf16_rope)
 constexpr int EPI_SWIGLU = 4;     // internal: [g | u] = X W_gu written to C, h = silu(g) * u written to aux
 constexpr int EPI_DSWIGLU = 5;    // internal: dh = dM W_down^T kept in registers, [dg | du] written to C, gu read from aux
@@ -535,7 +547,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
                                            : wk.n_blk * BN + static_cast<int>(rank) * 128;
         uint32_t tx = wk.narrow ? 2 * (Cfg::kABytes + Cfg::kBBytes / 2) : 2 * Cfg::kStageBytes;
         // measurement only: leave out the B (64) / A (128) operand loads to see how much of the mainloop is the L2 -> SM feed
-        const bool skip_b = (p.dbg & 64) != 0, skip_a = (p.dbg & 128) != 0 && !skip_b;  // never both: nothing would arm the barrier
+        const bool skip_b = PCV_DBG(p, 64), skip_a = PCV_DBG(p, 128) && !skip_b;  // never both: nothing would arm the barrier
         if (skip_b) tx -= wk.narrow ? Cfg::kBBytes : 2 * Cfg::kBBytes;
         if (skip_a) tx -= 2 * Cfg::kABytes;
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -617,10 +629,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     // once the store issued two puts earlier has read it, so one store is always in flight behind the math
     uint32_t put_box = 0;
     unsigned int pf0 = 0, pf1 = 0, pf2 = 0, pf3 = 0, pt = 0;  // profile: wait accumulator | wait operands | math | stores
-    const bool prof = p.prof != nullptr;
+    const bool prof = PCV_PROF(p);
     const unsigned int pstart = clk32();
     auto put = [&](const CUtensorMap* m, const uint4* q, int c0, int r0) {
-      if (p.dbg & 1) return;
+      if (PCV_DBG(p, 1)) return;
       const uint32_t bx = buf + put_box * Cfg::kEpiBoxBytes;
       if (lane == 0) tma_store_wait_read<Cfg::kEpiBoxes - 1>();  // the store that last used this box has read it
       __syncwarp();
@@ -628,7 +640,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       for (int v = 0; v < 8; ++v) st_shared_v4(bx + lane * 128 + ((v ^ sw) << 4), q[v]);
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0 && !(p.dbg & 32)) {
+      if (lane == 0 && !PCV_DBG(p, 32)) {
         if constexpr (EPI == PCV_EPI_F32_ATOMIC) tma_reduce_add_2d(m, bx, c0, r0);
         else tma_store_2d(m, bx, c0, r0);
         tma_store_commit();
@@ -660,7 +672,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         return false;
       };
       auto request = [&](int c, int r) {  // lane 0
-        if (p.dbg & 8) return;
+        if (PCV_DBG(p, 8)) return;
         mbar_expect_tx(ld_bar, 2 * Cfg::kEpiBoxBytes);
         tma_load_2d(box_g, &tma_x, ld_bar, c, r);
         tma_load_2d(box_u, &tma_bn, ld_bar, c, r);
@@ -690,7 +702,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           if (sl == 0 ? !has0 : !has1) continue;
           const bool last = (sl == 1) || !has1;
           uint4 pg[8], pu[8];
-          if (!(p.dbg & 8)) {
+          if (!PCV_DBG(p, 8)) {
             mbar_wait(ld_bar, ld_phase);
             ld_phase ^= 1u;
           }
@@ -714,7 +726,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             tmem_ld_32x32b_x32(taddr + sl * 64 + half * 32, r);
             tmem_ld_wait();
             if (last && half == 1) release();
-            if (p.dbg & 4) {
+            if (PCV_DBG(p, 4)) {
               pack32_bf16(r, p.alpha, pg + 4 * half);
               pack32_bf16(r, 2.f, pu + 4 * half);
             } else {
@@ -731,7 +743,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             for (int v = 0; v < 8; ++v) st_shared_v4(row_o + ((v ^ sw) << 4), o == 0 ? pg[v] : pu[v]);
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0 && !(p.dbg & 1)) {
+            if (lane == 0 && !PCV_DBG(p, 1)) {
               tma_store_2d(o == 0 ? &tma_c : &tma_c2, box_o, sl == 0 ? c0 : c1, row0);
               tma_store_commit();
             }
@@ -772,7 +784,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           tmem_ld_32x32b_x32(tg + 128 + c * 32, u);
           tmem_ld_wait();
           if (c == 1) release();
-          if (p.dbg & 4) {
+          if (PCV_DBG(p, 4)) {
             pack32_bf16(g, 1.f, qg + 4 * c);
             pack32_bf16(u, 1.f, qu + 4 * c);
             pack32_bf16(u, 2.f, qh + 4 * c);
@@ -784,7 +796,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         if (n0 < p.N) {
           put(&tma_c, qg, n0, row0);
           put(&tma_c2, qu, n0, row0);
-          if (!(p.dbg & 2)) put(&tma_x, qh, n0, row0);
+          if (!PCV_DBG(p, 2)) put(&tma_x, qh, n0, row0);
         }
         if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
       } else if constexpr (EPI == EPI_BF16_ROPE || EPI == PCV_EPI_BF16) {
@@ -845,10 +857,14 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       }
     }
     }  // EPI != EPI_DSWIGLU
+#ifdef PCV_MEASURE
     if (prof && lane == 0) {
       unsigned int* dst = p.prof + (static_cast<size_t>(blockIdx.x) * 8 + (warp - 4)) * 8;
       dst[0] = pf0; dst[1] = pf1; dst[2] = pf2; dst[3] = pf3; dst[4] = clk32() - pstart;
     }
+#else
+    (void)pf0; (void)pf1; (void)pf2; (void)pf3; (void)pstart;
+#endif
     if (lane == 0) tma_store_wait<0>();  // every box has left shared memory and reached global memory
     __syncwarp();
   }
@@ -1068,23 +1084,33 @@ static int auto_splits(int M, int N, int K) {
   return best;
 }
 
-static int g_gemm_mode = 0;  // 0 auto, 1 single-CTA tiles only, 2 CTA-pair tiles whenever legal
+// Process-wide tiling override (tests and A/B runs; every setting computes the same product): relaxed atomics.
+static std::atomic<int> g_gemm_mode{0};  // 0 auto, 1 single-CTA tiles only, 2 CTA-pair tiles whenever legal
+static std::atomic<int> g_gemm_tail{1};  // halve the tiles of a sparse last wave (pcv_gemm_set_mode(3 / 4): off / on)
+static std::atomic<long long> g_pair_launches{0};
+#ifdef PCV_MEASURE
 static int g_gemm_dbg = 0;
 static unsigned int* g_gemm_prof = nullptr;
-static int g_gemm_tail = 1;  // halve the tiles of a sparse last wave (pcv_gemm_set_mode(3 / 4) turns it off / on)
+#endif
 
 }  // namespace pcv
 
+#ifdef PCV_MEASURE
 extern "C" int pcv_gemm_set_profile(void* dev_buf) {
   pcv::g_gemm_prof = static_cast<unsigned int*>(dev_buf);
   return PCV_OK;
 }
+#endif
+
+extern "C" long long pcv_gemm_pair_launch_count(void) { return pcv::g_pair_launches.load(std::memory_order_relaxed); }
 
 extern "C" int pcv_gemm_set_mode(int mode) {
+#ifdef PCV_MEASURE
   if (mode >= 100 && mode < 356) { pcv::g_gemm_dbg = mode - 100; return PCV_OK; }
+#endif
   if (mode < 0 || mode > 4) return PCV_ERR_ARG;
-  if (mode >= 3) pcv::g_gemm_tail = mode == 4;
-  else pcv::g_gemm_mode = mode;
+  if (mode >= 3) pcv::g_gemm_tail.store(mode == 4, std::memory_order_relaxed);
+  else pcv::g_gemm_mode.store(mode, std::memory_order_relaxed);
   return PCV_OK;
 }
 
@@ -1107,7 +1133,8 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
     const int kps = (kb_total + splits - 1) / splits;
     const int sp = (kb_total + kps - 1) / kps;
     const long t2 = static_cast<long>(m2) * n2 * sp;
-    const bool pair = g_gemm_mode == 2 || (g_gemm_mode == 0 && t2 >= num_sms() / 2);
+    const int mode = g_gemm_mode.load(std::memory_order_relaxed);
+    const bool pair = mode == 2 || (mode == 0 && t2 >= num_sms() / 2);
     if (pair) {
       CUtensorMap ta, tb;
       int rc;
@@ -1135,12 +1162,14 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       // tail of the schedule: if the last wave would occupy at most half of the pairs, run its tiles as 256 x 128 halves
       p.full_tiles = static_cast<int>(t2);
       p.narrow = 0;
+#ifdef PCV_MEASURE
       p.dbg = g_gemm_dbg;
       p.prof = g_gemm_prof;
+#endif
       {
         const long np = num_sms() / 2;
         const long rem = t2 % np;
-        if (g_gemm_tail && sp == 1 && epilogue != PCV_EPI_F32_ATOMIC && t2 > np && rem > 0 && 2 * rem <= np) {
+        if (g_gemm_tail.load(std::memory_order_relaxed) && sp == 1 && epilogue != PCV_EPI_F32_ATOMIC && t2 > np && rem > 0 && 2 * rem <= np) {
           p.full_tiles = static_cast<int>(t2 - rem);
           p.narrow = 1;
           if (!b_mn_major) {
@@ -1151,6 +1180,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       }
       const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
       count_launch();
+      g_pair_launches.fetch_add(1, std::memory_order_relaxed);
       return dispatch_major_pair(a_mn_major, b_mn_major, epilogue, ta, tb, o, p, static_cast<int>(2 * pairs), st);
     }
   }
@@ -1239,11 +1269,14 @@ static int gemm_swiglu_impl(bool bwd, const void* A, const void* W, void* C, voi
   if (rc) return rc;
   p.full_tiles = p.m_tiles * p.n_tiles;
   p.narrow = 0;
+#ifdef PCV_MEASURE
   p.dbg = g_gemm_dbg;
   p.prof = g_gemm_prof;
+#endif
   const long t2 = static_cast<long>(p.m_tiles) * p.n_tiles;
   const long pairs = t2 < num_sms() / 2 ? t2 : num_sms() / 2;
   count_launch();
+  g_pair_launches.fetch_add(1, std::memory_order_relaxed);
   return dispatch_major_pair(0, bwd ? 0 : 1, bwd ? EPI_DSWIGLU : EPI_SWIGLU, ta, tb, o, p, static_cast<int>(2 * pairs),
                              static_cast<cudaStream_t>(stream));
 }

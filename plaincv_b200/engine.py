@@ -138,10 +138,16 @@ class Engine:
     def __init__(self, model, seq_len: Optional[int] = None, use_doc_mask: bool = False, process_group=None,
                  overlap: bool = True, grad_comm_dtype: torch.dtype = torch.bfloat16,
                  layers_per_bucket: Optional[int] = None):
+        """grad_comm_dtype: wire format of the gradient mean.  The default, bf16, is what BASELINE.json's north_star
+        asks for ("bucketed bf16 gradient all-reduce") and deviates from the reference's fp32 `lax.pmean`
+        (train_lm.py:207, 268) by one bf16 rounding of every bucket before and after the reduction: measured on
+        2/4/8 B200s the whole-buffer rel. L2 against the single-rank gradient of the same global batch stays below
+        4e-3 (bench.py `ddp_check`, tests/test_ddp_gpu.py); torch.float32 reproduces the reference's precision."""
         self.model = model
         self.seq_len = int(seq_len if seq_len is not None else model.cfg.seq_len)
         self.use_doc_mask = bool(use_doc_mask)
         self.overlap = overlap
+        self.pg = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         L = model.layout
         # buckets in the order their gradients become final during backward: head, layers L-1..0 (consecutive layers
@@ -178,7 +184,9 @@ class Engine:
             if self.use_doc_mask and batch.doc_start is None:
                 raise ValueError("Doc masking enabled but batch has no 'docs_lengths'.")  # train_lm.py:110
             return batch.inputs, batch.labels, (batch.doc_start if self.use_doc_mask else None)
-        inputs, labels, doc_start = prepare_batch(batch, self.seq_len, self.use_doc_mask)
+        # host dicts are range-checked here (token ids index the embedding table and the logits unchecked in the kernels);
+        # feed.BatchFeeder(vocab_size=...) does the same on its worker thread for staged batches
+        inputs, labels, doc_start = prepare_batch(batch, self.seq_len, self.use_doc_mask, self.model.cfg.vocab_size)
         dev = self.model.flat_grad.device
 
         def up(t):
@@ -254,7 +262,7 @@ class Engine:
         loss, acc = self.model.loss_and_acc(inputs, labels, doc_start=doc_start)
         stat = torch.stack([loss, acc])
         if self.world > 1:
-            dist.all_reduce(stat, op=dist.ReduceOp.SUM)
+            dist.all_reduce(stat, op=dist.ReduceOp.SUM, group=self.pg)
             stat = stat / self.world
         return stat[0], stat[1]
 

@@ -231,7 +231,13 @@ class BatchFeeder:
 
     def __init__(self, dataset: ArrowTokenDataset, micro_batch_size: int, seq_len: int, *, use_doc_mask: bool = False,
                  sampler: str = "sequential", sampler_seed: Optional[int] = None, start_idx: int = 0,
-                 device: Optional[torch.device] = None, depth: int = 3):
+                 device: Optional[torch.device] = None, depth: int = 3, reapply_start_idx: bool = True,
+                 vocab_size: Optional[int] = None):
+        """reapply_start_idx=True mirrors the reference's stateful samplers, whose `__iter__` skips the first
+        `start_idx * batch_size` samples on EVERY epoch after a resume, not only the first
+        (lm_datasampler.py:24-27, 59-63); False applies the offset to the first epoch only.
+        vocab_size, when given, makes the producer reject rows with token ids outside [0, vocab_size) — the kernels
+        index the embedding table and the logits with them unchecked."""
         if micro_batch_size <= 0 or len(dataset) < micro_batch_size:
             raise ValueError("dataset holds fewer rows than one micro-batch")
         self.ds, self.B, self.T = dataset, int(micro_batch_size), int(seq_len)
@@ -240,6 +246,10 @@ class BatchFeeder:
         self.device = torch.device(device) if device is not None else None
         self.cuda = self.device is not None and self.device.type == "cuda"
         self.depth = max(1, int(depth))
+        self.reapply_start_idx = bool(reapply_start_idx)
+        self.vocab_size = None if vocab_size is None else int(vocab_size)
+        if self.start_idx * self.B > len(dataset) - self.B:
+            raise ValueError("start_idx leaves less than one micro-batch in an epoch")
         self._rng = np.random.default_rng(int(sampler_seed)) if sampler in ("stateful_random", "random") and \
             sampler_seed is not None else None
         self._q: "queue.Queue" = queue.Queue(maxsize=self.depth)
@@ -249,6 +259,7 @@ class BatchFeeder:
         self.epoch, self.consumed = 0, self.start_idx
         n_buf = self.depth + 2  # staged + the one the consumer holds + the one being filled
         self._slots = []
+        self._slot_copy_done: List[Optional["torch.cuda.Event"]] = [None] * n_buf
         for k in range(n_buf):
             host = [torch.empty((self.B, self.T), dtype=torch.int32) for _ in range(3 if self.use_doc_mask else 2)]
             if self.cuda:
@@ -267,7 +278,7 @@ class BatchFeeder:
         first = True
         while True:
             order = epoch_indices(len(self.ds), self.sampler, batch_size=self.B, seed=self.seed,
-                                  start_idx=self.start_idx if first else 0, rng=self._rng)
+                                  start_idx=self.start_idx if (first or self.reapply_start_idx) else 0, rng=self._rng)
             first = False
             for k in range(len(order) // self.B):  # drop_last
                 yield order[k * self.B: (k + 1) * self.B]
@@ -287,7 +298,12 @@ class BatchFeeder:
                         continue
                 host, dev = self._slots[slot]
                 batch = self.ds.rows(idx)
-                inputs, labels, doc_start = prepare_batch(batch, self.T, self.use_doc_mask)
+                inputs, labels, doc_start = prepare_batch(batch, self.T, self.use_doc_mask, self.vocab_size)
+                # The slot's previous host -> device copy may still be QUEUED (the copy stream waits for the compute
+                # stream at every release): the pinned buffers must not be rewritten before it has actually run.
+                # Waiting here costs nothing: this is the worker thread.
+                if self._slot_copy_done[slot] is not None:
+                    self._slot_copy_done[slot].synchronize()
                 host[0].copy_(inputs)
                 host[1].copy_(labels)
                 if self.use_doc_mask:
@@ -299,6 +315,7 @@ class BatchFeeder:
                             d.copy_(h, non_blocking=True)
                         ready = torch.cuda.Event()
                         ready.record(self._copy_stream)
+                    self._slot_copy_done[slot] = ready
                 item = DeviceBatch(dev[0], dev[1], dev[2] if self.use_doc_mask else None, ready, slot)
                 while not self._stop.is_set():
                     try:
@@ -335,6 +352,10 @@ class BatchFeeder:
     def state(self) -> Dict[str, int]:
         per_epoch = len(self.ds) // self.B
         total = self.consumed
+        if self.reapply_start_idx and self.start_idx:
+            # every epoch of this stream is the tail [start_idx, per_epoch) (the reference's behaviour after a resume)
+            run, tail = total - self.start_idx, per_epoch - self.start_idx
+            return {"epoch": run // tail, "start_idx": self.start_idx + run % tail, "micro_batches": total}
         return {"epoch": total // per_epoch, "start_idx": total % per_epoch, "micro_batches": total}
 
     def close(self) -> None:

@@ -1,0 +1,39 @@
+"""torchrun worker of tests/test_ddp_gpu.py: one rank per GPU, NCCL.  Prints one JSON line per bucket-group size on
+rank 0 (plaincv_b200.selfcheck.ddp_gradient_check: N-rank gradients vs the whole global batch on one rank)."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from plaincv_b200.batch import synthetic_batch
+    from plaincv_b200.model import ModelConfig, Transformer
+    from plaincv_b200.selfcheck import ddp_gradient_check
+    use_doc = os.environ.get("PCV_TEST_DOC", "0") == "1"
+    n_layers = int(os.environ.get("PCV_TEST_LAYERS", "9"))
+    T, B, V = 1024, 2, 50280
+    cfg = ModelConfig(vocab_size=V, seq_len=T, dim=1024, expand=8 / 3, n_layers=n_layers, n_heads=16)
+    model = Transformer(cfg, device=dev, seed=0)  # same seed on every rank: identical replicas
+    batches = [synthetic_batch(B, T, V, seed=500 + k, doc_mean=300 if use_doc else None) for k in range(world)]
+    for lpb in (1, 4, 8):
+        res = ddp_gradient_check(model, T, use_doc, batches, rank, world, layers_per_bucket=lpb)
+        res["layers_per_bucket"] = lpb
+        if rank == 0:
+            print("DDPCHECK " + json.dumps(res), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -123,23 +123,52 @@ def test_feeder_yields_the_loader_loop(use_doc):
         f.close()
 
 
-def test_feeder_resumes_and_shuffles_like_the_stateful_sampler():
+@pytest.mark.parametrize("reapply", [True, False])
+def test_feeder_resumes_and_shuffles_like_the_stateful_sampler(reapply):
+    """Resume at start_idx = 2 with the persistent-Generator shuffle of StatefulRandomSampler
+    (lm_datasampler.py:33-66).  reapply_start_idx=True (default) is the reference's behaviour: `__iter__` slices
+    `indices[self.start:]` on EVERY epoch (:59-63); False applies the offset to the first epoch only."""
     ds = feed.ArrowTokenDataset(os.path.join(GOLD, "plain"))
     B, T = 3, 32
-    f = feed.BatchFeeder(ds, B, T, sampler="stateful_random", sampler_seed=9, start_idx=2)
+    f = feed.BatchFeeder(ds, B, T, sampler="stateful_random", sampler_seed=9, start_idx=2, reapply_start_idx=reapply)
     try:
         rng = np.random.default_rng(9)
         order = rng.permutation(np.arange(N, dtype=np.int64))[2 * B:]
         nxt = rng.permutation(np.arange(N, dtype=np.int64))
+        if reapply:
+            nxt = nxt[2 * B:]
         seq = [order[k * B:(k + 1) * B] for k in range(len(order) // B)] + [nxt[:B]]
         for rows in seq:
             item = next(f)
             assert torch.equal(item.inputs, torch.from_numpy(np.stack([_row_ids(i) for i in rows])[:, :-1].astype(np.int32)))
             f.release(item)
+        st = f.state()
+        assert st["micro_batches"] == 2 + len(seq) and st["epoch"] == 1
+        assert st["start_idx"] == (3 if reapply else 1)  # one batch into the second epoch
     finally:
         f.close()
     with pytest.raises(ValueError):
         feed.BatchFeeder(ds, 64, T)
+
+
+def test_token_ids_outside_the_vocabulary_are_rejected_on_the_host():
+    """ids index the embedding table / logits unchecked in the kernels, so the host contract rejects them."""
+    from plaincv_b200.batch import prepare_batch
+    ids = np.arange(2 * 9, dtype=np.int32).reshape(2, 9)
+    prepare_batch({"input_ids": ids}, 8, False, vocab_size=18)
+    with pytest.raises(ValueError, match="token ids must lie in"):
+        prepare_batch({"input_ids": ids}, 8, False, vocab_size=17)
+    neg = ids.copy()
+    neg[0, 0] = -1
+    with pytest.raises(ValueError, match="token ids must lie in"):
+        prepare_batch({"input_ids": neg}, 8, False, vocab_size=100)
+    ds = feed.InMemoryTokenDataset(np.full((4, 9), 50, dtype=np.int32))
+    f = feed.BatchFeeder(ds, 2, 8, vocab_size=50, depth=1)
+    try:
+        with pytest.raises(RuntimeError, match="producer failed"):
+            next(f)
+    finally:
+        f.close()
 
 
 def test_in_memory_dataset_feeds_like_the_arrow_one():

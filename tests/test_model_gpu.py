@@ -379,3 +379,31 @@ def test_feeder_device_batches_drive_the_engine(tmp_path, use_doc):
             assert rel_l2(g_f, model.flat_grad) < 1e-5  # same kernels, same inputs (fp32 reduce-add order only)
     finally:
         f.close()
+
+
+def test_feeder_never_refills_a_slot_before_its_copy_has_run():
+    """with the CPU far ahead of the GPU (no host sync in the loop, the compute stream held up by
+    a long kernel) the producer used to rewrite a slot's pinned buffers while that slot's earlier host -> device copy
+    was still queued behind the compute stream, so a step silently read a LATER batch.  Every step's inputs, as the
+    compute stream saw them, must be the dataset rows of that step."""
+    from plaincv_b200 import feed
+    T, B, V, n_rows = 64, 2, 1000, 64
+    raw = O.synthetic_batch(n_rows, T, V, seed=21)
+    ds = feed.InMemoryTokenDataset(raw["input_ids"])
+    dev = torch.device("cuda")
+    f = feed.BatchFeeder(ds, B, T, device=dev, depth=2, vocab_size=V)
+    seen = []
+    try:
+        torch.cuda._sleep(int(1.5e9))  # ~1 s: everything below is queued behind it, the host loop runs ahead
+        for k in range(24):
+            item = next(f)
+            seen.append(item.inputs.clone())  # on the compute stream, after the wait on the copy's event
+            f.release(item)
+        torch.cuda.synchronize()
+    finally:
+        f.close()
+    per_epoch = n_rows // B
+    for k, got in enumerate(seen):
+        rows = [(k % per_epoch) * B + j for j in range(B)]
+        want = torch.from_numpy(raw["input_ids"][rows][:, :-1].astype(np.int32))
+        assert torch.equal(got.cpu(), want), f"step {k} read another batch's tokens"

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Per-phase cycle counts of the CTA-pair GEMM epilogue warps (pcv_gemm_set_profile) at the 420M MLP shapes.
-GPU box only.  usage: python tools/prof_epilogue.py"""
+GPU box only; needs a measurement build: make -C plaincv_b200/csrc clean all XFLAGS=-DPCV_MEASURE.
+usage: python tools/prof_epilogue.py"""
 import os
 import sys
 
@@ -29,6 +30,8 @@ for name, fn in cases.items():
     fn()
     torch.cuda.synchronize()
     buf.zero_()
+    import ctypes
+    lib.pcv_gemm_set_profile.argtypes = [ctypes.c_void_p]  # -DPCV_MEASURE builds only
     lib.pcv_gemm_set_profile(buf.data_ptr())
     fn()
     torch.cuda.synchronize()
