@@ -331,33 +331,30 @@ class Workload:
         # PCV_DDP_OVERLAP=0 (A/B runs only): all-reduce the buckets after backward instead of under it
         # PCV_DDP_COMM=fp32 (A/B runs only): all-reduce the gradient buckets in fp32 instead of bf16
         self.comm_fp32 = os.environ.get("PCV_DDP_COMM", "bf16") == "fp32"
-        self.eng = Engine(self.model, seq_len=self.T, use_doc_mask=c["doc"],
+        # PCV_CUDA_GRAPH=0 (A/B runs only): launch every kernel from Python instead of replaying the captured step
+        self.cuda_graph = os.environ.get("PCV_CUDA_GRAPH", "1") != "0"
+        self.eng = Engine(self.model, seq_len=self.T, use_doc_mask=c["doc"], cuda_graph=self.cuda_graph,
                           overlap=os.environ.get("PCV_DDP_OVERLAP", "1") != "0",
                           grad_comm_dtype=torch.float32 if self.comm_fp32 else torch.bfloat16)
         self.batch = synthetic_batch(self.B, self.T, self.V, seed=1234 + rank, doc_mean=512 if c["doc"] else None)
         inputs_h, labels_h, ds_h = eng_prepare(self.eng, self.batch)
         self.inputs_d, self.labels_d = inputs_h.to(dev), labels_h.to(dev)
         self.ds_d = None if ds_h is None else ds_h.to(dev)
+        self.dev_batch = SimpleBatch(self.inputs_d, self.labels_d, self.ds_d)
         self.tokens_per_step = self.B * self.T * world
         self.fpt_causal = flops_per_token(c)
         self.fpt = gemm_flops_per_token(c) + attn_flops_per_token(c, self.batch.get("docs_lengths"))
 
     def step_resident(self):
-        model, eng = self.model, self.eng
-        model.sync_compute_weights()
-        eng.zero_grads_async()  # in stream order by default (a side-stream zero-fill under the forward measured 1 % slower)
-        eng._arm_hooks(True)
-        loss, acc = model.loss_and_acc(self.inputs_d, self.labels_d, doc_start=self.ds_d, unit_grad=True)
-        eng.wait_zero_grads()
-        loss.backward()
-        if self.world > 1:
-            eng.reducer.finish()
-        eng._arm_hooks(False)
+        """bf16 weight refresh + Engine.compute_grads on the device-resident batch (zero grads, fwd, bwd, N > 1: the
+        bucketed all-reduce under backward and the rank-mean of loss / acc)."""
+        self.model.sync_compute_weights()
+        loss, _ = self.eng.compute_grads(self.dev_batch)
         return loss
 
     def close(self):
         import torch
-        self.model = self.eng = self.inputs_d = self.labels_d = self.ds_d = None
+        self.model = self.eng = self.inputs_d = self.labels_d = self.ds_d = self.dev_batch = None
         torch.cuda.empty_cache()
 
 
@@ -505,8 +502,9 @@ def gpu_main(args) -> None:
                        "micro_batch_per_gpu": B, "parallelism": f"dp{world}", "params": model.count_params()[0],
                        "flop_per_token": fpt, "weights": "random-init (seed 100), fp32 masters + bf16 compute copies",
                        "l2": "working set per step (0.8 GB bf16 weights + ~13 GB activations at c3) >> 126 MB L2",
-                       "step": "zero grads + bf16 weight refresh + fwd + bwd + (N>1) bucketed "
-                               + ("fp32" if comm_fp32 else "bf16") + " gradient all-reduce under backward"},
+                       "step": "bf16 weight refresh + Engine.compute_grads (zero grads + fwd + bwd + (N>1) bucketed "
+                               + ("fp32" if comm_fp32 else "bf16") + " gradient all-reduce under backward)"
+                               + (", the micro-step replayed as one CUDA graph" if w.cuda_graph else "")},
             "mfu": {"of_burst_peak": tok_s * fpt / (world * peaks["bf16_tflops"] * 1e12),
                     "of_sustained_peak": tok_s * fpt / (world * peaks["bf16_tflops_sustained"] * 1e12),
                     "peaks": peaks["_source"]},

@@ -94,6 +94,15 @@ class GradReducer:
         else:
             self._handles.append((self._all_reduce_mean(t, async_op=True), None))
 
+    def finish_scalars(self) -> None:
+        """Make the compute stream (or the host, for CPU tensors) wait for reduce_scalars."""
+        if self.world == 1:
+            return
+        if self.cuda:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        else:
+            self._wait_handles()
+
     def finish(self) -> None:
         """Launch any bucket not yet launched, then make the compute stream wait for all of them."""
         if self.world == 1:
@@ -105,16 +114,57 @@ class GradReducer:
         if self.cuda:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         else:
-            for h, round_back in self._handles:
-                if isinstance(h, tuple):
-                    work, t = h
-                    work.wait()
-                    t.div_(self.world)
-                elif h is not None:
-                    h.wait()
-                if round_back is not None:
-                    round_back.copy_(round_back.to(torch.bfloat16).to(torch.float32))
-            self._handles = []
+            self._wait_handles()
+
+    def _wait_handles(self) -> None:
+        for h, round_back in self._handles:
+            if isinstance(h, tuple):
+                work, t = h
+                work.wait()
+                t.div_(self.world)
+            elif h is not None:
+                h.wait()
+            if round_back is not None:
+                round_back.copy_(round_back.to(torch.bfloat16).to(torch.float32))
+        self._handles = []
+
+
+class _GraphedMicro:
+    """One micro-step of an Engine captured as a CUDA graph (see Engine.__init__, cuda_graph).  Static int32 input
+    buffers; every replay is preceded by three small device-to-device copies into them."""
+
+    def __init__(self, eng: "Engine", key: tuple):
+        self.eng = eng
+        (self.shape, self.has_doc, self.accumulate, self.sync, self.loss_scale) = key
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        dev = eng.model.flat_grad.device
+        self.inputs = torch.zeros(self.shape, dtype=torch.int32, device=dev)
+        self.labels = torch.zeros(self.shape, dtype=torch.int32, device=dev)
+        self.doc = torch.zeros(self.shape, dtype=torch.int32, device=dev) if self.has_doc else None
+        self.stat = torch.zeros(2, dtype=torch.float32, device=dev)
+
+    def _stage(self, inputs, labels, doc_start) -> None:
+        self.inputs.copy_(inputs.view(self.shape), non_blocking=True)
+        self.labels.copy_(labels.view(self.shape), non_blocking=True)
+        if self.has_doc:
+            self.doc.copy_(doc_start.view(self.shape), non_blocking=True)
+
+    def run(self, inputs, labels, doc_start, stat: torch.Tensor) -> None:
+        eng = self.eng
+        self._stage(inputs, labels, doc_start)
+        if self.graph is None:
+            g = torch.cuda.CUDAGraph()
+            if eng._graph_pool is None:
+                eng._graph_pool = torch.cuda.graph_pool_handle()
+            # thread_local: other host threads (the BatchFeeder's worker stages the next batches meanwhile) may keep
+            # calling CUDA; autograd's device thread launches onto the capturing stream and is captured with it
+            with torch.cuda.graph(g, pool=eng._graph_pool, capture_error_mode="thread_local"):
+                self.stat.zero_()
+                eng._micro_body(self.inputs, self.labels, self.doc, self.accumulate, self.sync, self.loss_scale,
+                                self.stat)
+            self.graph = g
+        self.graph.replay()
+        stat += self.stat
 
 
 def bucket_groups(n_layers: int, layers_per_bucket: int) -> List[Tuple[int, int]]:
@@ -137,12 +187,18 @@ class Engine:
 
     def __init__(self, model, seq_len: Optional[int] = None, use_doc_mask: bool = False, process_group=None,
                  overlap: bool = True, grad_comm_dtype: torch.dtype = torch.bfloat16,
-                 layers_per_bucket: Optional[int] = None):
+                 layers_per_bucket: Optional[int] = None, cuda_graph: Optional[bool] = None):
         """grad_comm_dtype: wire format of the gradient mean.  The default, bf16, is what BASELINE.json's north_star
         asks for ("bucketed bf16 gradient all-reduce") and deviates from the reference's fp32 `lax.pmean`
         (train_lm.py:207, 268) by one bf16 rounding of every bucket before and after the reduction: measured on
         2/4/8 B200s the whole-buffer rel. L2 against the single-rank gradient of the same global batch stays below
-        4e-3 (bench.py `ddp_check`, tests/test_ddp_gpu.py); torch.float32 reproduces the reference's precision."""
+        4e-3 (bench.py `ddp_check`, tests/test_ddp_gpu.py); torch.float32 reproduces the reference's precision.
+
+        cuda_graph: replay one micro-step (zero grads, forward, backward, the side-stream wgrads and — N > 1 — the
+        bucketed all-reduce on the communication stream) as ONE CUDA graph instead of ~490 kernel launches issued
+        from Python: the first call of a given (batch shape, accumulate, sync, loss_scale) runs eagerly, the second
+        is captured, later ones replay.  Same kernels, same order, same results; what goes away is the GPU idling
+        between launches (about 2 ms of a 45 ms step at C3).  Default: env PCV_CUDA_GRAPH (off unless "1")."""
         self.model = model
         self.seq_len = int(seq_len if seq_len is not None else model.cfg.seq_len)
         self.use_doc_mask = bool(use_doc_mask)
@@ -163,6 +219,11 @@ class Engine:
         self.reducer = GradReducer(model.flat_grad, self._ranges, process_group, comm_dtype=grad_comm_dtype)
         self._zero_stream = None
         self._zero_pending = False
+        if cuda_graph is None:
+            cuda_graph = os.environ.get("PCV_CUDA_GRAPH", "0") == "1"
+        self.cuda_graph = bool(cuda_graph) and model.flat_grad.is_cuda
+        self._graphs: Dict[tuple, "_GraphedMicro"] = {}
+        self._graph_pool = None
 
     # ------------------------------------------------------------------ hooks
     def _arm_hooks(self, on: bool) -> None:
@@ -221,9 +282,11 @@ class Engine:
             torch.cuda.current_stream().wait_stream(self._zero_stream)
             self._zero_pending = False
 
-    def _micro(self, batch: dict, accumulate: bool, sync: bool, loss_scale: float, stat: torch.Tensor) -> None:
+    def _micro_body(self, inputs, labels, doc_start, accumulate: bool, sync: bool, loss_scale: float,
+                    stat: torch.Tensor) -> None:
+        """One micro-step on device tensors; `stat` (2 floats) receives += this rank's (loss, acc); the gradient buckets
+        are rank-averaged when sync (the two scalars are averaged by the caller, _reduce_stat, outside any graph)."""
         m = self.model
-        inputs, labels, doc_start = self._to_device(batch)
         if not accumulate:
             self.zero_grads_async()
         self._arm_hooks(sync)
@@ -233,9 +296,27 @@ class Engine:
         stat[0] += loss.detach()
         stat[1] += acc.detach()
         if sync and self.world > 1:
-            self.reducer.reduce_scalars(stat)
             self.reducer.finish()
         self._arm_hooks(False)
+
+    def _reduce_stat(self, stat: torch.Tensor) -> None:
+        """Rank-mean of the (loss, acc) sums (the pmean of train_lm.py:268-270 applied to the two scalars)."""
+        if self.world > 1:
+            self.reducer.reduce_scalars(stat)
+            self.reducer.finish_scalars()
+
+    def _micro(self, batch: dict, accumulate: bool, sync: bool, loss_scale: float, stat: torch.Tensor) -> None:
+        inputs, labels, doc_start = self._to_device(batch)
+        if not self.cuda_graph:
+            self._micro_body(inputs, labels, doc_start, accumulate, sync, loss_scale, stat)
+            return
+        key = (tuple(inputs.shape), doc_start is not None, bool(accumulate), bool(sync), float(loss_scale))
+        g = self._graphs.get(key)
+        if g is None:  # first call of this kind: eager (it is also the warm-up CUDA graphs need before a capture)
+            self._graphs[key] = _GraphedMicro(self, key)
+            self._micro_body(inputs, labels, doc_start, accumulate, sync, loss_scale, stat)
+            return
+        g.run(inputs, labels, doc_start, stat)
 
     def compute_grads(self, batch: dict, *, accumulate: bool = False, sync: bool = True, loss_scale: float = 1.0):
         """One micro-batch of fwd + bwd (train_lm.py:256-271).  Gradients land in model.flat_grad (param.grad are views):
@@ -243,6 +324,8 @@ class Engine:
         Returns (loss, acc) as 0-dim device tensors, rank-averaged when `sync`."""
         stat = torch.zeros(2, dtype=torch.float32, device=self.model.flat_grad.device)
         self._micro(batch, accumulate, sync, loss_scale, stat)
+        if sync:
+            self._reduce_stat(stat)
         return stat[0], stat[1]
 
     def train_step(self, micro_batches: Sequence[dict]):
@@ -253,6 +336,7 @@ class Engine:
         stat = torch.zeros(2, dtype=torch.float32, device=self.model.flat_grad.device)
         for k, mb in enumerate(micro_batches):
             self._micro(mb, accumulate=k > 0, sync=(k == n - 1), loss_scale=1.0 / n, stat=stat)
+        self._reduce_stat(stat)
         return stat[0] / n, stat[1] / n
 
     @torch.no_grad()

@@ -245,6 +245,8 @@ class BatchFeeder:
         self.sampler, self.seed, self.start_idx = sampler, sampler_seed, int(start_idx)
         self.device = torch.device(device) if device is not None else None
         self.cuda = self.device is not None and self.device.type == "cuda"
+        if self.cuda and self.device.index is None:  # the worker thread needs an explicit ordinal
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.depth = max(1, int(depth))
         self.reapply_start_idx = bool(reapply_start_idx)
         self.vocab_size = None if vocab_size is None else int(vocab_size)

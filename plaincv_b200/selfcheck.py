@@ -51,6 +51,19 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
     g_bf16_off, _ = run(grad_comm_dtype=torch.bfloat16, overlap=False)
     g_fp32, loss_ddp32 = run(grad_comm_dtype=torch.float32, overlap=True)
     g_fp32_off, _ = run(grad_comm_dtype=torch.float32, overlap=False)
+    # the same step replayed as a CUDA graph (forward, backward, side-stream wgrads, casts and NCCL all-reduces of the
+    # buckets on the communication stream, all captured): call 1 eager, call 2 captures, call 3 replays
+    g_graph, loss_graph = None, float("nan")
+    try:
+        eng_g = Engine(model, seq_len=seq_len, use_doc_mask=use_doc_mask, process_group=process_group,
+                       layers_per_bucket=layers_per_bucket, cuda_graph=True)
+        for _ in range(3):
+            lg, _ = eng_g.compute_grads(mine)
+        torch.cuda.synchronize()
+        g_graph, loss_graph = _snapshot(model), float(lg)
+        graph_err = None
+    except Exception as ex:  # reported, not fatal: the eager path is the reference for this check
+        graph_err = f"{type(ex).__name__}: {ex}"
 
     # the whole global batch on this rank alone, no communication
     solo = Engine(model, seq_len=seq_len, use_doc_mask=use_doc_mask, process_group=process_group,
@@ -69,6 +82,7 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
     vals = torch.tensor([
         _rel_l2(g_bf16, g_ref), _rel_l2(g_fp32, g_ref), _rel_l2(g_bf16_off, g_bf16), _rel_l2(g_fp32_off, g_fp32),
         _rel_l2(g_ref2, g_ref), abs(loss_ddp - loss_ref), abs(loss_ddp32 - loss_ref),
+        _rel_l2(g_graph, g_bf16) if g_graph is not None else float("inf"), abs(loss_graph - loss_ddp),
     ], dtype=torch.float64, device=model.flat_grad.device)
     # ranks must also agree with each other bit for bit after the all-reduce: compare a checksum of the averaged buffer
     csum = g_bf16.double().sum().reshape(1)
@@ -85,6 +99,7 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
         "rel_l2_overlap_off_vs_on_bf16": v[2], "rel_l2_overlap_off_vs_on_fp32": v[3],
         "rel_l2_rerun_noise": noise,
         "loss_abs_diff": v[5], "loss_abs_diff_fp32_wire": v[6],
+        "rel_l2_cuda_graph_vs_eager_bf16": v[7], "loss_abs_diff_cuda_graph": v[8], "cuda_graph_error": graph_err,
         "ranks_hold_identical_gradients": bool(float(cmin) == float(cmax)),
         "overlap_off_equal": bool(v[2] <= max(1e-5, 2.0 * noise) and v[3] <= max(1e-5, 2.0 * noise)),
         "ok": bool(v[0] <= 4e-3 and v[1] <= max(1e-5, 2.0 * noise) and v[5] <= 1e-4 and float(cmin) == float(cmax)),
