@@ -56,8 +56,36 @@ __device__ __forceinline__ float ex2f(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// 2^x on the FMA / ALU pipes instead of MUFU (the forward kernel is bound by the 16 exponentials per clock an SM's
+// MUFU units deliver, so a share of them is evaluated here): x is clamped to [-126, inf), split as x = n + f with
+// n = round(x) taken from the low mantissa bits of x + 1.5 * 2^23, f in [-0.5, 0.5], 2^f by a degree-4 polynomial
+// (max rel. error 4e-6 — two orders below the bf16 rounding of P) and n added into the exponent field.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -126.f);
+  const float xr = x + 12582912.f;               // 1.5 * 2^23: the integer part lands in the low mantissa bits
+  const float f = x - (xr - 12582912.f);
+  float p = fmaf(f, 9.6181291e-3f, 5.5504109e-2f);  // Taylor/minimax of 2^f around 0 on [-0.5, 0.5]
+  p = fmaf(p, f, 2.4022651e-1f);
+  p = fmaf(p, f, 6.9314718e-1f);
+  p = fmaf(p, f, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(xr) << 23));
+}
+#ifndef PCV_ATTN_POLY
+#define PCV_ATTN_POLY 0  // of every 8 exponentials in the forward softmax, this many take the polynomial
+#endif
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// tcgen05.wait::ld that also names the 32 destination registers of the load it completes, so no use of them can be
+// scheduled ahead of it (the loads below are issued one chunk ahead of their use)
+__device__ __forceinline__ void tmem_ld_wait_for(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                 "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
 }
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   uint4 v;
@@ -157,7 +185,9 @@ __device__ __forceinline__ void chunk_softmax(const uint32_t* sr, float c2, floa
   for (int k = 0; k < 32; k += 2) {
     const float s0 = __uint_as_float(sr[k]), s1 = __uint_as_float(sr[k + 1]);
     const float2 x = __ffma2_rn(make_float2(s0, s1), c2v, mbv);
-    float e0 = ex2f(x.x), e1 = ex2f(x.y);
+    // elements (k mod 8) < PCV_ATTN_POLY take the FMA-pipe polynomial, the rest MUFU.EX2
+    float e0 = ((k & 7) < PCV_ATTN_POLY) ? ex2_poly(x.x) : ex2f(x.x);
+    float e1 = (((k + 1) & 7) < PCV_ATTN_POLY) ? ex2_poly(x.y) : ex2f(x.y);
     if (MASK) {
       const bool v0 = (k >= lo && k <= hi), v1 = (k + 1 >= lo && k + 1 <= hi);
       e0 = v0 ? e0 : 0.f;
@@ -402,20 +432,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           const float mb = (ref == -INFINITY ? 0.f : ref) * c2;
           psum = make_float2(0.f, 0.f);
           float tile_max = -INFINITY;
-#pragma unroll 1
+          // the load of chunk c + 1 is in flight while chunk c is exponentiated (two register sets)
+          uint32_t sr[2][32];
+          tmem_ld_32x32b_x32(tS, sr[0]);
+          tmem_ld_wait_for(sr[0]);
+#pragma unroll
           for (int c = 0; c < 4; ++c) {
-            uint32_t sr[32];
-            tmem_ld_32x32b_x32(tS + c * 32, sr);
-            tmem_ld_wait();
+            if (c < 3) tmem_ld_32x32b_x32(tS + (c + 1) * 32, sr[(c + 1) & 1]);
             uint32_t pk[16];
-            if (need_mask) chunk_softmax<true, true>(sr, c2, mb, lo0 - c * 32, hi0 - c * 32, pk, psum, tile_max);
-            else chunk_softmax<false, true>(sr, c2, mb, 0, 0, pk, psum, tile_max);
+            if (need_mask) chunk_softmax<true, true>(sr[c & 1], c2, mb, lo0 - c * 32, hi0 - c * 32, pk, psum, tile_max);
+            else chunk_softmax<false, true>(sr[c & 1], c2, mb, 0, 0, pk, psum, tile_max);
             if (!pv_waited) {  // P_w in tensor memory is still being read by the previous tile's P.V until this fires
               mbar_wait(bPVdone(w), (i - 1) & 1);
               tc_fence_after();
               pv_waited = true;
             }
             tmem_st_32x32b_x16(tP + c * 16, pk);
+            if (c < 3) tmem_ld_wait_for(sr[(c + 1) & 1]);
           }
           if (!check) break;
           const bool bad = !((tile_max - ref) * c2 <= 60.f);

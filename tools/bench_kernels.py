@@ -7,6 +7,9 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch  # noqa: E402
 
+from plaincv_b200 import _lib  # noqa: E402
+if os.environ.get("PCV_KB_LIB"):  # A/B builds of the library (tools/ab/*.so), measurement only
+    _lib.LIB_PATH = os.path.abspath(os.environ["PCV_KB_LIB"])
 from plaincv_b200 import ops  # noqa: E402
 
 dev = "cuda"
