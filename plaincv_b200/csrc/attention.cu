@@ -45,7 +45,7 @@ __device__ __forceinline__ long long gtimer() {
 #define TRACE(slot, idx) do { } while (0)
 #endif
 
-constexpr int kAttnThreads = 320;     // forward
+constexpr int kAttnThreads = 192;     // forward: softmax warpgroup + producer + MMA issuer
 constexpr int kAttnBwdThreads = 512;  // backward: 2 compute warpgroups, 1 dQ warpgroup, producer + MMA warps
 constexpr int kTileBytes = 128 * 128;  // 128 rows x 64 bf16
 constexpr float kLog2e = 1.4426950408889634f;
@@ -167,12 +167,15 @@ __device__ __forceinline__ void chunk_p_ds(const uint32_t* sr, const uint32_t* p
 
 // ================================================================================================ forward
 struct AttnFwdSmem {
-  static constexpr int kQ = 0;                          // 2 tiles
-  static constexpr int kK = kQ + 2 * kTileBytes;        // 3 slots
-  static constexpr int kV = kK + 3 * kTileBytes;        // 3 slots
-  static constexpr int kBar = kV + 3 * kTileBytes;      // barriers
+  static constexpr int kSlots = 2;                          // K / V ring depth
+  static constexpr int kQ = 0;                              // 1 tile (doubles as the staging tile of O at the end)
+  static constexpr int kK = kQ + kTileBytes;                // kSlots tiles
+  static constexpr int kV = kK + kSlots * kTileBytes;       // kSlots tiles
+  static constexpr int kBar = kV + kSlots * kTileBytes;     // barriers
   static constexpr int kBytes = kBar + 256 + 1024;
 };
+// two CTAs per SM: 2 x (dynamic + 1 KB system reservation) must fit in 227 KB
+static_assert(2 * (AttnFwdSmem::kBytes + 1024) <= 232448, "attn_fwd: two CTAs must fit in one SM's shared memory");
 
 // 32 score columns of one row: p = exp2(s*c2 - mb) (0 outside [lo, hi] when MASK), packed to bf16 pairs.
 // Accumulates the row sum into `sum2` (two partial sums) and, when TRACK, the largest valid score into `smax`.
@@ -201,36 +204,45 @@ __device__ __forceinline__ void chunk_softmax(const uint32_t* sr, float c2, floa
   }
 }
 
-// Forward CTA (320 threads) = one (batch, head, 256-query block); q, k in `qkv` are already rotated (RoPE is applied
-// by the QKV GEMM epilogue, pcv_gemm_bf16_rope, or by pcv_rope_qk):
-//   warps 0-3 / 4-7 : softmax warpgroup 0 / 1, one thread per query row of its 128-row tile.  One pass over S per
-//                     tile: the exponent reference is the row max of the row's first visible tile and is only moved
-//                     if a later score exceeds it by 2^60 (everything is floating point: a stale reference costs no
-//                     precision), so P.V accumulates in TMEM across key tiles with no per-tile rescale or read-back.
-//   warp 8          : TMA producer (Q once, K / V ring of 3 slots each) + TMEM allocation
-//   warp 9          : tcgen05.mma issuer: S_w = Q_w.K_j^T, O_w += P_w.V_j, ping-ponged between the warpgroups
-// TMEM: S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384) P0 [384,448) P1 [448,512) (bf16 pairs).
-__global__ void __launch_bounds__(kAttnThreads, 1)
+// Forward CTA (192 threads) = one (batch, head, 128-query tile); TWO CTAs are resident per SM (256 of the 512
+// tensor-memory columns and 82 KB of shared memory each), so one CTA's prologue (barrier set-up, tensor-memory
+// allocation, first loads) and epilogue run under the other CTA's exponentials (the former 256-query CTA spent 3.5 us
+// of fixed cost per CTA, 18 % of the kernel, overlapped with nothing).
+// Keys are processed in HALF tiles of 64 with the scores double-buffered in tensor memory: S(h+1) = Q.K^T is computed
+// while the warpgroup exponentiates S(h), so the softmax warps never wait for the tensor pipe (with one 128-key S
+// buffer they idled ~500 of every 2700 cycles, and two CTAs with equal periods stay phase-locked: the exponent units
+// (MUFU, the bound of this kernel: 16 / clock / SM) were 74 % busy in steady state).
+// q, k in `qkv` are already rotated (RoPE is applied by the QKV GEMM epilogue, pcv_gemm_bf16_rope, or by pcv_rope_qk):
+//   warps 0-3 : softmax warpgroup, one thread per query row.  One pass over S per half tile: the exponent reference is
+//               the row max of the row's first visible half tile and is only moved if a later row sum shows that a
+//               score exceeded it by ~2^64 (everything is floating point: a stale reference costs no precision), so
+//               P.V accumulates in tensor memory across key tiles with no per-tile rescale or read-back.  The
+//               tensor-memory load of score chunk 1 is in flight while chunk 0 is exponentiated.
+//   warp 4    : TMA producer (Q once, K / V rings of 2 x 128-key tiles) + tensor-memory allocation
+//   warp 5    : tcgen05.mma issuer: S(h) = Q.K_h^T (128 x 64 x 64), O += P(h).V_h (128 x 64 x 64)
+// TMEM (256 columns): S0 [0,64) S1 [64,128) O [128,192) P0 [192,224) P1 [224,256) (P: bf16 pairs).
+__global__ void __launch_bounds__(kAttnThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_out, const int32_t* __restrict__ doc_start,
                 __nv_bfloat16* __restrict__ out, float* __restrict__ lse, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
+  constexpr int kSlots = AttnFwdSmem::kSlots;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sQ = sbase + AttnFwdSmem::kQ, sK = sbase + AttnFwdSmem::kK, sV = sbase + AttnFwdSmem::kV,
                  sBar = sbase + AttnFwdSmem::kBar;
-  const uint32_t bQ = sBar;                                     // (tx)
-  auto bKfull = [&](int s) { return sBar + 8u * (1 + s); };     // [3] (tx)
-  auto bVfull = [&](int s) { return sBar + 8u * (4 + s); };     // [3] (tx)
-  auto bKempty = [&](int s) { return sBar + 8u * (7 + s); };    // [3] (1, commit)
-  auto bVempty = [&](int s) { return sBar + 8u * (10 + s); };   // [3] (1, commit)
-  auto bSfull = [&](int w) { return sBar + 8u * (13 + w); };    // [2] (1, commit)
-  auto bPfull = [&](int w) { return sBar + 8u * (15 + w); };    // [2] (128)
-  auto bPVdone = [&](int w) { return sBar + 8u * (17 + w); };   // [2] (1, commit)
-  const uint32_t tmem_ptr_smem = sBar + 8u * 19;
+  const uint32_t bQ = sBar;                                                // (tx)
+  auto bKfull = [&](int s) { return sBar + 8u * (1 + s); };                // [kSlots] (tx)
+  auto bVfull = [&](int s) { return sBar + 8u * (1 + kSlots + s); };       // [kSlots] (tx)
+  auto bKempty = [&](int s) { return sBar + 8u * (1 + 2 * kSlots + s); };  // [kSlots] (1, commit)
+  auto bVempty = [&](int s) { return sBar + 8u * (1 + 3 * kSlots + s); };  // [kSlots] (1, commit)
+  auto bSfull = [&](int u) { return sBar + 8u * (1 + 4 * kSlots + u); };   // [2] (1, commit)
+  auto bPfull = [&](int u) { return sBar + 8u * (3 + 4 * kSlots + u); };   // [2] (128)
+  auto bPVdone = [&](int u) { return sBar + 8u * (5 + 4 * kSlots + u); };  // [2] (1, commit)
+  const uint32_t tmem_ptr_smem = sBar + 8u * (7 + 4 * kSlots);
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 #ifdef PCV_TRACE
-  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 288);
+  const bool trace_on = (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) && ((threadIdx.x & 127) == 0 || threadIdx.x == 160);
   const int cta_lin = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
   if (tid == 0 && cta_lin < 4096) {
     unsigned int smid;
@@ -239,76 +251,64 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     g_cta_trace[cta_lin * 4 + 2] = smid;
   }
 #endif
-  // launch order = blockIdx.x fastest, z slowest: every (head, batch) pair of the heaviest (latest) query block first,
-  // the lightest blocks last, so that the SMs run dry within one short CTA of each other
-  const int n_qblk = gridDim.z;
-  const int qblk = n_qblk - 1 - blockIdx.z;
+  // launch order = blockIdx.x fastest, z slowest: every (head, batch) pair of the heaviest (latest) query tile first,
+  // the lightest tiles last, so that the SMs run dry within one short CTA of each other
+  const int n_qt = gridDim.z;
+  const int qt = n_qt - 1 - blockIdx.z;
   const int h = blockIdx.x, b = blockIdx.y;
   const int d = NH * 64;
-  const int q0 = qblk * 256;
+  const int q0 = qt * 128;
   const long seq_row0 = static_cast<long>(b) * T;
 
-  // per-warpgroup key-tile ranges [jmin_w, jmax_w]
-  int jmin[2], jmax[2];
-#pragma unroll
-  for (int w = 0; w < 2; ++w) {
-    const int r0 = q0 + 128 * w;
-    if (r0 < T) {
-      jmax[w] = r0 / 128;
-      jmin[w] = doc_start ? (doc_start[seq_row0 + r0] / 128) : 0;
-    } else {
-      jmax[w] = -1;
-      jmin[w] = 0;
-    }
-  }
-  const int jlo = jmin[0];
-  const int jhi = jmax[1] >= 0 ? jmax[1] : jmax[0];
-  auto active = [&](int w, int j) { return j >= jmin[w] && j <= jmax[w]; };
+  // key tiles [jlo, jhi] visible to this query tile: causal, and not before the first row's document
+  const int jhi = qt;
+  const int jlo = doc_start ? (doc_start[seq_row0 + q0] / 128) : 0;
+  const int n_it = jhi - jlo + 1;
+  const int n_ht = 2 * n_it;  // half tiles of 64 keys
 
-  if (warp == 8 && lane == 0) {
+  if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_out);
     mbar_init(bQ, 1);
-    for (int s = 0; s < 3; ++s) {
+    for (int s = 0; s < kSlots; ++s) {
       mbar_init(bKfull(s), 1);
       mbar_init(bVfull(s), 1);
       mbar_init(bKempty(s), 1);
       mbar_init(bVempty(s), 1);
     }
-    for (int w = 0; w < 2; ++w) {
-      mbar_init(bSfull(w), 1);
-      mbar_init(bPfull(w), 128);
-      mbar_init(bPVdone(w), 1);
+    for (int u = 0; u < 2; ++u) {
+      mbar_init(bSfull(u), 1);
+      mbar_init(bPfull(u), 128);
+      mbar_init(bPVdone(u), 1);
     }
     fence_mbar_init();
     // Q and the first K / V tile are requested right away: their latency runs under the tensor-memory allocation and
     // the block-wide barrier below
     const int row0 = static_cast<int>(seq_row0);
-    const int nq = jmax[1] >= 0 ? 2 : 1;
-    mbar_expect_tx(bQ, nq * kTileBytes);
-    for (int w = 0; w < nq; ++w) tma_load_2d(sQ + w * kTileBytes, &tm_qkv, bQ, h * 64, row0 + q0 + 128 * w);
+    mbar_expect_tx(bQ, kTileBytes);
+    tma_load_2d(sQ, &tm_qkv, bQ, h * 64, row0 + q0);
     mbar_expect_tx(bKfull(0), kTileBytes);
     tma_load_2d(sK, &tm_qkv, bKfull(0), d + h * 64, row0 + jlo * 128);
     mbar_expect_tx(bVfull(0), kTileBytes);
     tma_load_2d(sV, &tm_qkv, bVfull(0), 2 * d + h * 64, row0 + jlo * 128);
   }
-  if (warp == 8) {
+  if (warp == 4) {
     __syncwarp();
-    tmem_alloc<512>(tmem_ptr_smem);
+    tmem_alloc<256>(tmem_ptr_smem);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
 
-  if (warp == 8) {
+  if (warp == 4) {
     // ============================== TMA producer ==============================
     if (lane == 0) {
       const int row0 = static_cast<int>(seq_row0);
       int idx = 1;
       for (int j = jlo + 1; j <= jhi; ++j, ++idx) {
-        const int slot = idx % 3;
-        const uint32_t par = (idx / 3) & 1;
+        const int slot = idx % kSlots;
+        const uint32_t par = (idx / kSlots) & 1;
         TRACE(6, idx * 3 + 0);
         mbar_wait(bKempty(slot), par ^ 1u);
         mbar_expect_tx(bKfull(slot), kTileBytes);
@@ -321,215 +321,205 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
+  } else if (warp == 5) {
     // ============================== MMA issuer ==============================
     {
       const uint32_t lead = elect_one_sync();
       const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
-      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64, false, false);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64, false, true);
-      auto issue_S = [&](int w, int slot) {
+      // S(hh) = Q . K[64 keys of half tile hh]^T -> score buffer hh & 1
+      auto issue_S = [&](int hh) {
+        const int i = hh >> 1, sub = hh & 1, slot = i % kSlots;
+        if (sub == 0) {
+          mbar_wait(bKfull(slot), (i / kSlots) & 1);
+          tc_fence_after();
+        }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          const uint64_t da = umma_smem_desc(sQ + w * kTileBytes + k * 32, 16, 1024);
-          const uint64_t db = umma_smem_desc(sK + slot * kTileBytes + k * 32, 16, 1024);
-          umma_bf16_ss_p(tb + w * 128, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
+          const uint64_t da = umma_smem_desc(sQ + k * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sK + slot * kTileBytes + sub * 8192 + k * 32, 16, 1024);
+          umma_bf16_ss_p(tb + (hh & 1) * 64, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
         }
-        tc_commit_p(bSfull(w), lead);
+        tc_commit_p(bSfull(hh & 1), lead);
+        if (sub == 1) tc_commit_p(bKempty(slot), lead);  // both halves of this K tile have been read
       };
-      auto issue_PV = [&](int w, int slot, bool accumulate) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          // A = P_w straight from tensor memory (bf16 pairs, 8 columns per 16 keys); B = V (MN-major: one 128-byte
-          // row per key).  P never touches shared memory, whose bandwidth the S / P.V operand reads already fill.
-          const uint64_t db = umma_smem_desc(sV + slot * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ts_p(tb + 256 + w * 64, tb + 384 + w * 64 + k * 8, db, idesc_pv,
-                         (accumulate || k > 0) ? 1u : 0u, lead);
+      // O += P(hh) . V[64 keys of half tile hh]
+      auto issue_PV = [&](int hh) {
+        const int i = hh >> 1, sub = hh & 1, slot = i % kSlots;
+        if (sub == 0) {
+          mbar_wait(bVfull(slot), (i / kSlots) & 1);
+          tc_fence_after();
         }
-        tc_commit_p(bPVdone(w), lead);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          // A = P straight from tensor memory (bf16 pairs, 8 columns per 16 keys); B = V (MN-major: one 128-byte
+          // row per key).  P never touches shared memory.
+          const uint64_t db = umma_smem_desc(sV + slot * kTileBytes + sub * 8192 + k * 2048, kTileBytes, 1024);
+          umma_bf16_ts_p(tb + 128, tb + 192 + (hh & 1) * 32 + k * 8, db, idesc_pv, (hh > 0 || k > 0) ? 1u : 0u, lead);
+        }
+        tc_commit_p(bPVdone(hh & 1), lead);
+        if (sub == 1) tc_commit_p(bVempty(slot), lead);
       };
       mbar_wait(bQ, 0);
-      mbar_wait(bKfull(0), 0);
       tc_fence_after();
-#pragma unroll
-      for (int w = 0; w < 2; ++w)
-        if (active(w, jlo)) issue_S(w, 0);
-      tc_commit_p(bKempty(0), lead);
-      int idx = 0;
-      for (int j = jlo; j <= jhi; ++j, ++idx) {
-        const int slot = idx % 3;
-        const uint32_t par = (idx / 3) & 1;
-        const int slot1 = (idx + 1) % 3;
-#pragma unroll
-        for (int w = 0; w < 2; ++w) {
-          const bool act = active(w, j);
-          const bool nxt = (j + 1 <= jhi) && active(w, j + 1);
-          const int i = j - jmin[w];
-          if (act) {
-            TRACE(4 + w, i * 2 + 0);
-            mbar_wait(bPfull(w), i & 1);  // P_w(j) is in shared memory and S_w has been consumed
-            TRACE(4 + w, i * 2 + 1);
-          }
-          if (nxt) {  // next S first: it is what the softmax warpgroup waits for
-            mbar_wait(bKfull(slot1), ((idx + 1) / 3) & 1);
-            tc_fence_after();
-            issue_S(w, slot1);
-          }
-          if (act) {
-            mbar_wait(bVfull(slot), par);
-            tc_fence_after();
-            issue_PV(w, slot, i > 0);
-          }
-        }
-        if (j + 1 <= jhi) tc_commit_p(bKempty(slot1), lead);  // every S that reads K(j+1) has been issued
-        tc_commit_p(bVempty(slot), lead);
+      issue_S(0);
+      issue_S(1);
+      for (int hh = 0; hh < n_ht; ++hh) {
+        TRACE(4, hh * 2 + 0);
+        mbar_wait(bPfull(hh & 1), (hh >> 1) & 1);  // P(hh) is in tensor memory and S buffer hh & 1 has been consumed
+        tc_fence_after();
+        TRACE(4, hh * 2 + 1);
+        issue_PV(hh);
+        if (hh + 2 < n_ht) issue_S(hh + 2);
       }
     }
     __syncwarp();
   } else {
-    // ============================== softmax warpgroups ==============================
-    const int w = warp >> 2;
-    const int r = tid & 127;
-    if (jmax[w] >= 0) {
-      const int t = q0 + 128 * w + r;
-      const int ds_t = doc_start ? doc_start[seq_row0 + min(t, T - 1)] : 0;
-      const int ds_hi = doc_start ? doc_start[seq_row0 + min(q0 + 128 * w + 127, T - 1)] : 0;
-      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-      const uint32_t tS = tmem_base + lane_off + w * 128;
-      const uint32_t tO = tmem_base + lane_off + 256 + w * 64;
-      const uint32_t tP = tmem_base + lane_off + 384 + w * 64;
-      constexpr float c2 = kSoftmaxScale * kLog2e;
-      float ref = -INFINITY, l_run = 0.f;
-      const int n_it = jmax[w] - jmin[w] + 1;
-      for (int i = 0; i < n_it; ++i) {
-        const int j = jmin[w] + i;
-        TRACE(w * 2 + 0, i * 4 + 0);
-        mbar_wait(bSfull(w), i & 1);
-        tc_fence_after();
-        TRACE(w * 2 + 0, i * 4 + 1);
-        const bool need_mask = (j * 128 + 127 > q0 + 128 * w) || (j * 128 < ds_hi);
-        const int key0 = j * 128;
-        const int hi0 = t - key0, lo0 = ds_t - key0;  // valid key window relative to the tile start
-        // rows that have not seen a visible key yet take their reference from this tile's row max (first pass)
-        const bool first = __any_sync(0xffffffffu, ref == -INFINITY);
-        if (first) {
-          float rmax = -INFINITY;
+    // ============================== softmax warpgroup ==============================
+    const int r = tid;
+    const int t = q0 + r;
+    const int ds_t = doc_start ? doc_start[seq_row0 + min(t, T - 1)] : 0;
+    const int ds_hi = doc_start ? doc_start[seq_row0 + min(q0 + 127, T - 1)] : 0;
+    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    const uint32_t tO = tmem_base + lane_off + 128;
+    constexpr float c2 = kSoftmaxScale * kLog2e;
+    constexpr float kSumLimit = 1.8446744e19f;  // 2^64: a row sum beyond it means a score left the reference's range
+    float ref = -INFINITY, l_run = 0.f;
+    for (int hh = 0; hh < n_ht; ++hh) {
+      const int u = hh & 1;
+      const uint32_t tS = tmem_base + lane_off + u * 64;
+      const uint32_t tP = tmem_base + lane_off + 192 + u * 32;
+      const int key0 = (jlo + (hh >> 1)) * 128 + u * 64;
+      TRACE(0, hh * 4 + 0);
+      mbar_wait(bSfull(u), (hh >> 1) & 1);
+      tc_fence_after();
+      TRACE(0, hh * 4 + 1);
+      const bool need_mask = (key0 + 63 > q0) || (key0 < ds_hi);
+      const int hi0 = t - key0, lo0 = ds_t - key0;  // valid key window relative to the half tile's first key
+      // row max of this half tile (masked): the reference of rows that have not seen a visible key yet, and the new
+      // reference when a row sum overflows the range of the old one
+      auto row_max = [&]() {
+        float rmax = -INFINITY;
 #pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            uint32_t sr[32];
-            tmem_ld_32x32b_x32(tS + c * 32, sr);
-            tmem_ld_wait();
-            rmax = need_mask ? chunk_rowmax<true>(sr, lo0 - c * 32, hi0 - c * 32, rmax)
-                             : chunk_rowmax<false>(sr, 0, 0, rmax);
-          }
-          if (ref == -INFINITY) ref = rmax;
+        for (int c = 0; c < 2; ++c) {
+          uint32_t sr[32];
+          tmem_ld_32x32b_x32(tS + c * 32, sr);
+          tmem_ld_wait();
+          rmax = need_mask ? chunk_rowmax<true>(sr, lo0 - c * 32, hi0 - c * 32, rmax)
+                           : chunk_rowmax<false>(sr, 0, 0, rmax);
         }
-        TRACE(w * 2 + 0, i * 4 + 2);
-        bool pv_waited = (i == 0);
-        bool check = !first;
-        float2 psum;
-        while (true) {
-          const float mb = (ref == -INFINITY ? 0.f : ref) * c2;
-          psum = make_float2(0.f, 0.f);
-          float tile_max = -INFINITY;
-          // the load of chunk c + 1 is in flight while chunk c is exponentiated (two register sets)
-          uint32_t sr[2][32];
-          tmem_ld_32x32b_x32(tS, sr[0]);
-          tmem_ld_wait_for(sr[0]);
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (c < 3) tmem_ld_32x32b_x32(tS + (c + 1) * 32, sr[(c + 1) & 1]);
-            uint32_t pk[16];
-            if (need_mask) chunk_softmax<true, true>(sr[c & 1], c2, mb, lo0 - c * 32, hi0 - c * 32, pk, psum, tile_max);
-            else chunk_softmax<false, true>(sr[c & 1], c2, mb, 0, 0, pk, psum, tile_max);
-            if (!pv_waited) {  // P_w in tensor memory is still being read by the previous tile's P.V until this fires
-              mbar_wait(bPVdone(w), (i - 1) & 1);
-              tc_fence_after();
-              pv_waited = true;
-            }
-            tmem_st_32x32b_x16(tP + c * 16, pk);
-            if (c < 3) tmem_ld_wait_for(sr[(c + 1) & 1]);
-          }
-          if (!check) break;
-          const bool bad = !((tile_max - ref) * c2 <= 60.f);
-          if (!__any_sync(0xffffffffu, bad)) break;
-          // a score beyond 2^60 of the reference: move the reference, rescale what has been accumulated, redo the tile
-          const float ref_new = fmaxf(ref, tile_max);
-          const float alpha = ex2f((ref - ref_new) * c2);
+        return rmax;
+      };
+      const bool first = __any_sync(0xffffffffu, ref == -INFINITY);
+      if (first) {
+        const float rmax = row_max();
+        if (ref == -INFINITY) ref = rmax;
+      }
+      TRACE(0, hh * 4 + 2);
+      bool pv_waited = (hh < 2);
+      bool check = true;  // (rows that just took their reference from this half tile pass trivially)
+      float2 psum;
+      while (true) {
+        const float mb = (ref == -INFINITY ? 0.f : ref) * c2;
+        psum = make_float2(0.f, 0.f);
+        float unused_max = 0.f;
+        // the load of chunk 1 is in flight while chunk 0 is exponentiated
+        uint32_t s0[32], s1[32], pk[16];
+        tmem_ld_32x32b_x32(tS, s0);
+        tmem_ld_wait_for(s0);
+        tmem_ld_32x32b_x32(tS + 32, s1);
+        if (need_mask) chunk_softmax<true, false>(s0, c2, mb, lo0, hi0, pk, psum, unused_max);
+        else chunk_softmax<false, false>(s0, c2, mb, 0, 0, pk, psum, unused_max);
+        if (!pv_waited) {  // P buffer u is still being read by P.V of half tile hh - 2 until this fires
+          mbar_wait(bPVdone(u), ((hh >> 1) - 1) & 1);
           tc_fence_after();
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            uint32_t orr[16];
-            tmem_ld_32x32b_x16(tO + c * 16, orr);
-            tmem_ld_wait();
-#pragma unroll
-            for (int k = 0; k < 16; ++k) orr[k] = __float_as_uint(__uint_as_float(orr[k]) * alpha);
-            tmem_st_32x32b_x16(tO + c * 16, orr);
-          }
-          tmem_st_wait();
-          l_run *= alpha;
-          ref = ref_new;
-          check = false;
+          pv_waited = true;
         }
-        l_run += psum.x + psum.y;
-        tmem_st_wait();
-        tc_fence_before();
-        mbar_arrive(bPfull(w));
-        TRACE(w * 2 + 0, i * 4 + 3);
-      }
-      // ---- epilogue: O is complete in TMEM; normalise, store
-      {
-        mbar_wait(bPVdone(w), (n_it - 1) & 1);
+        tmem_st_32x32b_x16(tP, pk);
+        tmem_ld_wait_for(s1);
+        if (need_mask) chunk_softmax<true, false>(s1, c2, mb, lo0 - 32, hi0 - 32, pk, psum, unused_max);
+        else chunk_softmax<false, false>(s1, c2, mb, 0, 0, pk, psum, unused_max);
+        tmem_st_32x32b_x16(tP + 16, pk);
+        if (!check) break;
+        const bool bad = !(psum.x + psum.y <= kSumLimit);
+        if (!__any_sync(0xffffffffu, bad)) break;
+        // a score far beyond the reference: move the reference to this half tile's row max, rescale what has been
+        // accumulated (every P.V issued so far must have completed first), redo the half tile
+        const float ref_new = fmaxf(ref, row_max());
+        const float alpha = ex2f((ref - ref_new) * c2);
+        if (hh >= 1) mbar_wait(bPVdone((hh - 1) & 1), ((hh - 1) >> 1) & 1);
         tc_fence_after();
-        const float inv_l = 1.f / l_run;
-        uint32_t o0[32], o1[32];
-        tmem_ld_32x32b_x32(tO, o0);
-        tmem_ld_32x32b_x32(tO + 32, o1);
-        tmem_ld_wait();
-        // the 128 x 64 output tile leaves through this warpgroup's Q tile (all its S MMAs are long done) and one TMA
-        // store: whole 128-byte rows, nothing for the CTA's last instructions to wait on but the read of the tile
-        {
-          const uint32_t orow = sQ + w * kTileBytes + r * 128;
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            uint4 o;
-            o.x = pack_bf16x2(__uint_as_float(o0[v * 8 + 0]) * inv_l, __uint_as_float(o0[v * 8 + 1]) * inv_l);
-            o.y = pack_bf16x2(__uint_as_float(o0[v * 8 + 2]) * inv_l, __uint_as_float(o0[v * 8 + 3]) * inv_l);
-            o.z = pack_bf16x2(__uint_as_float(o0[v * 8 + 4]) * inv_l, __uint_as_float(o0[v * 8 + 5]) * inv_l);
-            o.w = pack_bf16x2(__uint_as_float(o0[v * 8 + 6]) * inv_l, __uint_as_float(o0[v * 8 + 7]) * inv_l);
-            st_shared_v4(orow + ((v ^ (r & 7)) << 4), o);
-          }
+        for (int c = 0; c < 4; ++c) {
+          uint32_t orr[16];
+          tmem_ld_32x32b_x16(tO + c * 16, orr);
+          tmem_ld_wait();
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            uint4 o;
-            o.x = pack_bf16x2(__uint_as_float(o1[v * 8 + 0]) * inv_l, __uint_as_float(o1[v * 8 + 1]) * inv_l);
-            o.y = pack_bf16x2(__uint_as_float(o1[v * 8 + 2]) * inv_l, __uint_as_float(o1[v * 8 + 3]) * inv_l);
-            o.z = pack_bf16x2(__uint_as_float(o1[v * 8 + 4]) * inv_l, __uint_as_float(o1[v * 8 + 5]) * inv_l);
-            o.w = pack_bf16x2(__uint_as_float(o1[v * 8 + 6]) * inv_l, __uint_as_float(o1[v * 8 + 7]) * inv_l);
-            st_shared_v4(orow + (((4 + v) ^ (r & 7)) << 4), o);
-          }
-          fence_proxy_async_smem();
-          named_bar_sync(1 + w, 128);
-          if (r == 0) {
-            tma_store_2d(&tm_out, sQ + w * kTileBytes, h * 64, static_cast<int>(seq_row0) + q0 + 128 * w);
-            tma_store_commit();
-          }
-          if (t < T) lse[(static_cast<long>(b) * NH + h) * T + t] = ref * kSoftmaxScale + logf(l_run);
-          if (r == 0) tma_store_wait_read<0>();  // shared memory is given up when the CTA exits
+          for (int k = 0; k < 16; ++k) orr[k] = __float_as_uint(__uint_as_float(orr[k]) * alpha);
+          tmem_st_32x32b_x16(tO + c * 16, orr);
         }
+        tmem_st_wait();
+        l_run *= alpha;
+        ref = ref_new;
+        check = false;
       }
+      l_run += psum.x + psum.y;
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(bPfull(u));
+      TRACE(0, hh * 4 + 3);
+    }
+    // ---- epilogue: O is complete in TMEM; normalise, store
+    {
+      mbar_wait(bPVdone((n_ht - 1) & 1), ((n_ht - 1) >> 1) & 1);  // MMAs complete in order: this is the last one
+      tc_fence_after();
+      const float inv_l = 1.f / l_run;
+      uint32_t o0[32], o1[32];
+      tmem_ld_32x32b_x32(tO, o0);
+      tmem_ld_32x32b_x32(tO + 32, o1);
+      tmem_ld_wait();
+      // the 128 x 64 output tile leaves through the Q tile (all S MMAs are long done) and one TMA store: whole
+      // 128-byte rows, nothing for the CTA's last instructions to wait on but the read of the tile
+      const uint32_t orow = sQ + r * 128;
+#pragma unroll
+      for (int v = 0; v < 4; ++v) {
+        uint4 o;
+        o.x = pack_bf16x2(__uint_as_float(o0[v * 8 + 0]) * inv_l, __uint_as_float(o0[v * 8 + 1]) * inv_l);
+        o.y = pack_bf16x2(__uint_as_float(o0[v * 8 + 2]) * inv_l, __uint_as_float(o0[v * 8 + 3]) * inv_l);
+        o.z = pack_bf16x2(__uint_as_float(o0[v * 8 + 4]) * inv_l, __uint_as_float(o0[v * 8 + 5]) * inv_l);
+        o.w = pack_bf16x2(__uint_as_float(o0[v * 8 + 6]) * inv_l, __uint_as_float(o0[v * 8 + 7]) * inv_l);
+        st_shared_v4(orow + ((v ^ (r & 7)) << 4), o);
+      }
+#pragma unroll
+      for (int v = 0; v < 4; ++v) {
+        uint4 o;
+        o.x = pack_bf16x2(__uint_as_float(o1[v * 8 + 0]) * inv_l, __uint_as_float(o1[v * 8 + 1]) * inv_l);
+        o.y = pack_bf16x2(__uint_as_float(o1[v * 8 + 2]) * inv_l, __uint_as_float(o1[v * 8 + 3]) * inv_l);
+        o.z = pack_bf16x2(__uint_as_float(o1[v * 8 + 4]) * inv_l, __uint_as_float(o1[v * 8 + 5]) * inv_l);
+        o.w = pack_bf16x2(__uint_as_float(o1[v * 8 + 6]) * inv_l, __uint_as_float(o1[v * 8 + 7]) * inv_l);
+        st_shared_v4(orow + (((4 + v) ^ (r & 7)) << 4), o);
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+      if (r == 0) {
+        tma_store_2d(&tm_out, sQ, h * 64, static_cast<int>(seq_row0) + q0);
+        tma_store_commit();
+      }
+      if (t < T) lse[(static_cast<long>(b) * NH + h) * T + t] = ref * kSoftmaxScale + logf(l_run);
+      if (r == 0) tma_store_wait_read<0>();  // shared memory is given up when the CTA exits
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == 4) {
     tc_fence_after();
-    tmem_dealloc<512>(tmem_base);
+    tmem_dealloc<256>(tmem_base);
   }
 #ifdef PCV_TRACE
   if (tid == 0 && cta_lin < 4096) {
     g_cta_trace[cta_lin * 4 + 1] = gtimer();
-    g_cta_trace[cta_lin * 4 + 3] = jhi - jlo + 1;
+    g_cta_trace[cta_lin * 4 + 3] = n_it;
   }
 #endif
 }
@@ -1081,7 +1071,7 @@ extern "C" int pcv_attn_fwd(const void* qkv, const int32_t* doc_start, void* out
     if (e != cudaSuccess) return static_cast<int>(e);
     attr = true;
   }
-  dim3 grid(n_heads, B, (T + 255) / 256);
+  dim3 grid(n_heads, B, T / 128);
   attn_fwd_kernel<<<grid, kAttnThreads, AttnFwdSmem::kBytes, static_cast<cudaStream_t>(stream)>>>(
       tm, tm_out, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
   count_launch();

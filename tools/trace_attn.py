@@ -45,23 +45,21 @@ lib.pcv_debug_read_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
 print("rc", lib.pcv_debug_read_trace(buf, 8192))
 a = np.array(buf[:], dtype=np.int64).reshape(8, 1024)
 t0 = a[0, 0]
-for w in range(2):
-    print(f"--- softmax WG{w}: per tile [wait_S, pass1, pass2+arrive, fold+loop] cycles; abs start")
-    s = a[w * 2]
-    n = 17 if w == 1 else 16
-    for i in range(n):
-        x = s[i * 4:i * 4 + 5]
-        print(i, x[1] - x[0], x[2] - x[1], x[3] - x[2], (x[4] - x[3]) if i + 1 < n else -1, "  @", x[0] - t0)
-for w in range(2):
-    m = a[4 + w]
-    print(f"--- MMA waits for P of WG{w}: [wait cycles] @abs")
-    print([(int(m[i * 2 + 1] - m[i * 2]), int(m[i * 2] - t0)) for i in range(16)])
+print("--- fwd CTA (0,0,0) = heaviest query tile, softmax warpgroup: per 64-key half tile [wait_S, pass1, pass2+arrive, loop] cycles; abs start")
+s = a[0]
+n = 2 * (T // 128)
+for i in range(n):
+    x = s[i * 4:i * 4 + 5]
+    print(i, x[1] - x[0], x[2] - x[1], x[3] - x[2], (x[4] - x[3]) if i + 1 < n else -1, "  @", x[0] - t0)
+m = a[4]
+print("--- MMA waits for P: [wait cycles] @abs")
+print([(int(m[i * 2 + 1] - m[i * 2]), int(m[i * 2] - t0)) for i in range(n)])
 
 ld = a[6]
 print("--- fwd loader (thread 256): per K tile [wait empty slot, load+rope+store] @abs")
 print([(int(ld[i * 3 + 1] - ld[i * 3]), int(ld[i * 3 + 2] - ld[i * 3 + 1]), int(ld[i * 3] - t0)) for i in range(16)])
 
-cta_report('fwd', B * NH * ((T + 255) // 256))
+cta_report('fwd', B * NH * (T // 128))
 
 # ---- backward
 dout = torch.randn(B * T, d, device="cuda").to(torch.bfloat16)
