@@ -565,12 +565,30 @@ struct AttnBwdSmem {
   static constexpr int kBar = kdQ + 2 * kTileBytes;
   static constexpr int kBytes = kBar + 256 + 1024;
 };
+static_assert(AttnBwdSmem::kBytes <= 232448, "attn_bwd shared memory");
 
 template <uint32_t N>
 __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <uint32_t N>
 __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
+// Backward CTA (512 threads), PERSISTENT: a CTA works on one (batch, head, 128-key tile) item after the other.  Its
+// first item is its own blockIdx; further ones are taken from the CTAs of the grid that have not been launched yet
+// (cluster launch control: the hardware cancels such a CTA and hands its blockIdx over), so the grid's launch order —
+// per sequence, longest loops first — is the work queue and nothing is scheduled statically.  Tensor memory, barriers
+// and descriptors are set up once per CTA, and across an item boundary the next item's K / V / Q / dO loads and its
+// first S / dP MMAs run while the compute warps still write the finished item's dK / dV (one CTA per item spent
+// 6.2k cycles before its first tile and 4.9k after its last: 27 % of the kernel at the 420M shape).
+//   warps 0-7  : compute — thread (r, half) owns query row r, 64 of the 128 key columns of a tile:
+//                S, dP (tensor memory) -> P = exp2(S*c - lse), dS = P*(dP - delta)*scale -> shared memory (P, dS: the
+//                MN-major A operands of dV += P^T.dO, dK += dS^T.Q) and tensor memory (dS: the A operand of dQ = dS.K);
+//                after an item's last tile: dK (un-rotated) and dV -> bf16 -> shared memory -> TMA store
+//   warps 8-11 : dQ warpgroup — dQ of every tile from tensor memory through an fp32 staging tile and a TMA reduce-add
+//   warp 12    : TMA producer (K, V per item; Q / dO ring of 3; the rotation-table rows of the key tile take one more
+//                turn of the ring) and the work-stealing requests
+//   warp 13    : tcgen05.mma issuer
+// TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448) dS(bf16 pairs) [448,512).
+// Barrier phases: `g` counts tiles over the CTA's whole life, `ring` counts turns of the Q / dO ring, `k` counts items.
 __global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                 const __grid_constant__ CUtensorMap tm_dq, const __grid_constant__ CUtensorMap tm_cs,
@@ -578,22 +596,26 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                 const int32_t* __restrict__ doc_start, const float* __restrict__ lse, const float* __restrict__ delta,
                 float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int T, int NH) {
   extern __shared__ uint8_t smem_raw[];
+  constexpr int kStages = AttnBwdSmem::kStages;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV, sQ = sbase + AttnBwdSmem::kQ,
                  sdO = sbase + AttnBwdSmem::kdO, sP = sbase + AttnBwdSmem::kP, sdS = sbase + AttnBwdSmem::kdS,
                  sBar = sbase + AttnBwdSmem::kBar;
-  const uint32_t bKVfull = sBar;                                // (tx: K and V)
-  auto bQdOfull = [&](int s) { return sBar + 8u * (1 + s); };   // [3] (tx: Q_i and dO_i)
-  auto bStageEmpty = [&](int s) { return sBar + 8u * (4 + s); };  // [3] (1, commit)
-  const uint32_t bSdPfull = sBar + 8u * 8;                      // (1, commit)
-  const uint32_t bPdSfull = sBar + 8u * 9;                      // (256)
-  const uint32_t bdQfull = sBar + 8u * 10;                      // (1, commit)
-  const uint32_t bdQempty = sBar + 8u * 11;                     // (128)
-  const uint32_t bAccFull = sBar + 8u * 12;                     // (1, commit) dK/dV complete
+  const uint32_t bKVfull = sBar;                                  // (tx: K and V)                      per item
+  auto bQdOfull = [&](int s) { return sBar + 8u * (1 + s); };     // [3] (tx: Q_i and dO_i)             per ring turn
+  auto bStageEmpty = [&](int s) { return sBar + 8u * (4 + s); };  // [3] (1: commit, or the tail's arrive)
+  const uint32_t bSdPfull = sBar + 8u * 8;                        // (1, commit)                        per tile
+  const uint32_t bPdSfull = sBar + 8u * 9;                        // (256)                              per tile
+  const uint32_t bdQfull = sBar + 8u * 10;                        // (1, commit)                        per tile
+  const uint32_t bdQempty = sBar + 8u * 11;                       // (128)                              per tile
+  const uint32_t bAccFull = sBar + 8u * 12;                       // (1, commit) dK/dV complete          per item
   const uint32_t tmem_ptr_smem = sBar + 8u * 13;
-  const uint32_t bSdPfree = sBar + 8u * 14;                     // (256) S / dP of a tile are in registers
-  const uint32_t bPfree = sBar + 8u * 15;                       // (1, commit) dV MMAs done: P in shared memory is free
-  const uint32_t bCSfull = sBar + 8u * 16;                      // (tx) rotation table rows of the key tile
+  const uint32_t bSdPfree = sBar + 8u * 14;                       // (256) S / dP of a tile are in registers
+  const uint32_t bPfree = sBar + 8u * 15;                         // (1, commit) dV MMAs done: P in shared memory is free
+  const uint32_t bAccFree = sBar + 8u * 17;                       // (256) dK / dV have left tensor memory, per item
+  const uint32_t bStaged = sBar + 8u * 18;                        // (1) the dK / dV stores have read the P buffer, per item
+  auto bItem = [&](int u) { return sBar + 8u * (19 + u); };       // [2] (tx: 16 bytes) answer of the work-stealing request
+  auto sItem = [&](int u) { return sBar + 8u * 22 + 16u * u; };   // [2] x 16 bytes, 16-byte aligned
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -606,31 +628,47 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     g_cta_trace[cta_lin * 4 + 0] = gtimer();
     g_cta_trace[cta_lin * 4 + 2] = smid;
   }
+  int trace_items = 0;
 #endif
-  TRACE(6, 5);
-  // launch order (x fastest, z slowest): per sequence, key tile 0 of every head first (all query tiles visible: the
-  // longest loop), the one-tile loops last.  Sequences stay apart so that the fp32 dQ accumulator lines the reduce-adds
-  // hit (8 MB per sequence) stay in L2 instead of cycling through it.
-  const int j = blockIdx.y;
-  const int h = blockIdx.x, b = blockIdx.z;
   const int d = NH * 64;
-  const long seq_row0 = static_cast<long>(b) * T;
   const int n_qt = (T + 127) / 128;
-  const int key0 = j * 128;
-  // query tiles that can see this key tile: i >= j (causal) and doc_start[first row of tile i] <= last key of tile j
-  const int i_lo = j;
-  int i_hi = n_qt - 1;
-  if (doc_start) {
-    const int key_last = min(key0 + 127, T - 1);
-    // doc_start is non-decreasing in t: binary search the last tile whose first row's document starts <= key_last
-    int lo = j, hi = n_qt - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (doc_start[seq_row0 + mid * 128] <= key_last) lo = mid; else hi = mid - 1;
+
+  // An item = (h, j, b) in blockIdx terms.  Launch order (x fastest, z slowest): per sequence, key tile 0 of every head
+  // first (all query tiles visible: the longest loop), the one-tile loops last.
+  struct Item {
+    int h, j, b, i_lo, n_it, key0;
+    long seq_row0;
+  };
+  auto make_item = [&](int x, int y, int z) {
+    Item w;
+    w.h = x; w.j = y; w.b = z;
+    w.seq_row0 = static_cast<long>(z) * T;
+    w.key0 = y * 128;
+    // query tiles that can see this key tile: i >= j (causal) and doc_start[first row of tile i] <= last key of tile j
+    w.i_lo = y;
+    int i_hi = n_qt - 1;
+    if (doc_start) {
+      const int key_last = min(w.key0 + 127, T - 1);
+      // doc_start is non-decreasing in t: binary search the last tile whose first row's document starts <= key_last
+      int lo = y, hi = n_qt - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (doc_start[w.seq_row0 + mid * 128] <= key_last) lo = mid; else hi = mid - 1;
+      }
+      i_hi = lo;
     }
-    i_hi = lo;
-  }
-  const int n_it = i_hi - i_lo + 1;
+    w.n_it = i_hi - w.i_lo + 1;  // >= 1: tile j always sees itself
+    return w;
+  };
+  // item k + 1 of this CTA: the answer to the request issued while item k was loaded (every role reads it itself)
+  auto next_item = [&](int k_next, Item& w) -> bool {
+    mbar_wait(bItem(k_next & 1), ((k_next - 1) >> 1) & 1);  // slot 1: items 1, 3, 5 ...; slot 0: items 2, 4, 6 ...
+    int x, y, z;
+    if (!clc_query(sItem(k_next & 1), x, y, z)) return false;
+    w = make_item(x, y, z);
+    return true;
+  };
+  Item first = make_item(blockIdx.x, blockIdx.y, blockIdx.z);
 
   if (warp == 12 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
@@ -639,7 +677,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tma_prefetch_desc(&tm_cs);
     tma_prefetch_desc(&tm_dqkv);
     mbar_init(bKVfull, 1);
-    for (int s = 0; s < AttnBwdSmem::kStages; ++s) {
+    for (int s = 0; s < kStages; ++s) {
       mbar_init(bQdOfull(s), 1);
       mbar_init(bStageEmpty(s), 1);
     }
@@ -647,22 +685,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(bPdSfull, 256);
     mbar_init(bSdPfree, 256);
     mbar_init(bPfree, 1);
-    mbar_init(bCSfull, 1);
     mbar_init(bdQfull, 1);
     mbar_init(bdQempty, 128);
     mbar_init(bAccFull, 1);
+    mbar_init(bAccFree, 256);
+    mbar_init(bStaged, 1);
+    mbar_init(bItem(0), 1);
+    mbar_init(bItem(1), 1);
     fence_mbar_init();
-    // K, V and the first Q / dO tile are requested right away: their latency runs under the tensor-memory allocation
-    // and the block-wide barrier below
-    const int row0 = static_cast<int>(seq_row0);
+    // K, V and the first Q / dO tile of the first item are requested right away: their latency runs under the
+    // tensor-memory allocation and the block-wide barrier below
+    const int row0 = static_cast<int>(first.seq_row0);
     mbar_expect_tx(bKVfull, 2 * kTileBytes);
-    tma_load_2d(sK, &tm_qkv, bKVfull, d + h * 64, row0 + key0);
-    tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + h * 64, row0 + key0);
-    if (n_it > 0) {
-      mbar_expect_tx(bQdOfull(0), 2 * kTileBytes);
-      tma_load_2d(sQ, &tm_qkv, bQdOfull(0), h * 64, row0 + i_lo * 128);
-      tma_load_2d(sdO, &tm_do, bQdOfull(0), h * 64, row0 + i_lo * 128);
-    }
+    tma_load_2d(sK, &tm_qkv, bKVfull, d + first.h * 64, row0 + first.key0);
+    tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + first.h * 64, row0 + first.key0);
+    mbar_expect_tx(bQdOfull(0), 2 * kTileBytes);
+    tma_load_2d(sQ, &tm_qkv, bQdOfull(0), first.h * 64, row0 + first.i_lo * 128);
+    tma_load_2d(sdO, &tm_do, bQdOfull(0), first.h * 64, row0 + first.i_lo * 128);
   }
   if (warp == 12) {
     __syncwarp();
@@ -676,28 +715,47 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                  tdS = tmem_base + 448;  // dS as bf16 pairs: the A operand of dQ = dS.K, read from tensor memory
 
   if (warp >= 12) {
-    reg_dealloc<40>();  // warpgroup 3: producer, MMA issuer, two idle warps
+    reg_dealloc<56>();  // warpgroup 3: producer, MMA issuer, two idle warps (8 x 168 + 4 x 96 + 4 x 56 registers per lane: 62464 of 65536)
   }
   if (warp == 12) {
     // ============================== TMA producer (q, k in qkv are already rotated) ==============================
     if (lane == 0) {
-      const int row0 = static_cast<int>(seq_row0);
-      for (int it = 1; it < n_it; ++it) {
-        const int i = i_lo + it;
-        const int stage = it % 3;
-        mbar_wait(bStageEmpty(stage), ((it / 3) & 1) ^ 1u);
-        mbar_expect_tx(bQdOfull(stage), 2 * kTileBytes);
-        tma_load_2d(sQ + stage * kTileBytes, &tm_qkv, bQdOfull(stage), h * 64, row0 + i * 128);
-        tma_load_2d(sdO + stage * kTileBytes, &tm_do, bQdOfull(stage), h * 64, row0 + i * 128);
-      }
-      if (n_it > 0) {
-        // one more turn of the ring: (cos, sin) of the 128 key rows, for the transposed rotation of dK at the end —
-        // fetched two tiles ahead of its use instead of from global memory when every SM's tail is waiting on L2
-        const int stage = n_it % 3;
-        mbar_wait(bStageEmpty(stage), ((n_it / 3) & 1) ^ 1u);
-        mbar_expect_tx(bCSfull, 2 * kTileBytes);
-        tma_load_2d(sQ + stage * kTileBytes, &tm_cs, bCSfull, 0, key0);     // pairs 0..15  (compute half 0)
-        tma_load_2d(sdO + stage * kTileBytes, &tm_cs, bCSfull, 32, key0);   // pairs 16..31 (compute half 1)
+      Item w = first;
+      int ring = 0;
+      for (int k = 0;; ++k) {
+        const int row0 = static_cast<int>(w.seq_row0);
+        if (k > 0) {
+          // sK / sV are read by every MMA of the previous item: free once its last ones have completed
+          mbar_wait(bAccFull, (k - 1) & 1);
+          mbar_expect_tx(bKVfull, 2 * kTileBytes);
+          tma_load_2d(sK, &tm_qkv, bKVfull, d + w.h * 64, row0 + w.key0);
+          tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + w.h * 64, row0 + w.key0);
+        }
+        // ask for the item after this one now: the answer is there long before it is needed
+        mbar_expect_tx(bItem((k + 1) & 1), 16);
+        clc_try_cancel(sItem((k + 1) & 1), bItem((k + 1) & 1));
+        for (int it = (k == 0 ? 1 : 0); it < w.n_it; ++it) {
+          const int i = w.i_lo + it;
+          const int rr = ring + it;
+          const int stage = rr % kStages;
+          mbar_wait(bStageEmpty(stage), ((rr / kStages) & 1) ^ 1u);
+          mbar_expect_tx(bQdOfull(stage), 2 * kTileBytes);
+          tma_load_2d(sQ + stage * kTileBytes, &tm_qkv, bQdOfull(stage), w.h * 64, row0 + i * 128);
+          tma_load_2d(sdO + stage * kTileBytes, &tm_do, bQdOfull(stage), w.h * 64, row0 + i * 128);
+        }
+        ring += w.n_it;
+        {
+          // one more turn of the ring: (cos, sin) of the 128 key rows, for the transposed rotation of dK at the end —
+          // fetched two tiles ahead of its use instead of from global memory when every SM's tail is waiting on L2
+          const int stage = ring % kStages;
+          mbar_wait(bStageEmpty(stage), ((ring / kStages) & 1) ^ 1u);
+          // (signalled on the stage's own full barrier, like every turn of the ring, so that its phases keep counting turns)
+          mbar_expect_tx(bQdOfull(stage), 2 * kTileBytes);
+          tma_load_2d(sQ + stage * kTileBytes, &tm_cs, bQdOfull(stage), 0, w.key0);     // pairs 0..15  (compute half 0)
+          tma_load_2d(sdO + stage * kTileBytes, &tm_cs, bQdOfull(stage), 32, w.key0);   // pairs 16..31 (compute half 1)
+          ++ring;
+        }
+        if (!next_item(k + 1, w)) break;
       }
     }
     __syncwarp();
@@ -710,110 +768,125 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);   // S, dP
       constexpr uint32_t idesc_kv = umma_idesc_bf16(128, 64, true, true);     // dV = P^T.dO, dK = dS^T.Q
       constexpr uint32_t idesc_dq = umma_idesc_bf16(128, 64, false, true);    // dQ = dS.K
-      mbar_wait(bKVfull, 0);
-      tc_fence_after();
       auto issue_SdP = [&](int stage) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t da = umma_smem_desc(sQ + stage * kTileBytes + k * 32, 16, 1024);
-          const uint64_t db = umma_smem_desc(sK + k * 32, 16, 1024);
-          umma_bf16_ss_p(tS, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t da = umma_smem_desc(sQ + stage * kTileBytes + kk * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sK + kk * 32, 16, 1024);
+          umma_bf16_ss_p(tS, da, db, idesc_s, kk > 0 ? 1u : 0u, lead);
         }
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t da = umma_smem_desc(sdO + stage * kTileBytes + k * 32, 16, 1024);
-          const uint64_t db = umma_smem_desc(sV + k * 32, 16, 1024);
-          umma_bf16_ss_p(tdP, da, db, idesc_s, k > 0 ? 1u : 0u, lead);
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t da = umma_smem_desc(sdO + stage * kTileBytes + kk * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(sV + kk * 32, 16, 1024);
+          umma_bf16_ss_p(tdP, da, db, idesc_s, kk > 0 ? 1u : 0u, lead);
         }
         tc_commit_p(bSdPfull, lead);
       };
-      if (n_it > 0) {
-        mbar_wait(bQdOfull(0), 0);
-        tc_fence_after();
-        issue_SdP(0);
-      }
-      for (int it = 0; it < n_it; ++it) {
-        const int stage = it % 3;
-        const uint32_t sPb = sP, sdSb = sdS;
-        TRACE(4, it * 2 + 0);
-        // next tile's S and dP first: they are what the compute warps wait for.  They may overwrite S / dP as soon as
-        // every compute thread holds its part of tile `it` in registers — about half of that tile's math still to go,
-        // which is what hides the latency of these MMAs
-        if (it + 1 < n_it) {
-          const int s1 = (it + 1) % 3;
-          mbar_wait(bQdOfull(s1), ((it + 1) / 3) & 1);
-          mbar_wait(bSdPfree, it & 1);
+      Item w = first;
+      int g = 0, ring = 0;
+      for (int k = 0;; ++k) {
+        mbar_wait(bKVfull, k & 1);
+        {
+          // first S / dP of the item: its operands have landed and the previous tile's S / dP are in registers
+          const int stage = ring % kStages;
+          mbar_wait(bQdOfull(stage), (ring / kStages) & 1);
+          if (g > 0) mbar_wait(bSdPfree, (g - 1) & 1);
           tc_fence_after();
-          TRACE(5, it * 4 + 0);
-          issue_SdP(s1);
-          TRACE(5, it * 4 + 1);
+          issue_SdP(stage);
         }
-        mbar_wait(bPdSfull, it & 1);  // P/dS(it) are in shared memory and tensor memory
-        tc_fence_after();
-        TRACE(4, it * 2 + 1);
-        mbar_wait(bdQempty, (it & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
-        tc_fence_after();
-        TRACE(5, it * 4 + 2);
+        for (int it = 0; it < w.n_it; ++it, ++g) {
+          const int rr = ring + it;
+          const int stage = rr % kStages;
+          TRACE(4, it * 2 + 0);
+          // next tile's S and dP first: they are what the compute warps wait for.  They may overwrite S / dP as soon as
+          // every compute thread holds its part of this tile in registers — about half of the tile's math still to go,
+          // which is what hides the latency of these MMAs
+          if (it + 1 < w.n_it) {
+            const int s1 = (rr + 1) % kStages;
+            mbar_wait(bQdOfull(s1), ((rr + 1) / kStages) & 1);
+            mbar_wait(bSdPfree, g & 1);
+            tc_fence_after();
+            TRACE(5, it * 4 + 0);
+            issue_SdP(s1);
+            TRACE(5, it * 4 + 1);
+          }
+          mbar_wait(bPdSfull, g & 1);  // P / dS of this tile are in shared memory and tensor memory
+          tc_fence_after();
+          TRACE(4, it * 2 + 1);
+          mbar_wait(bdQempty, (g & 1) ^ 1u);  // previous tile's dQ has been read out of TMEM
+          // a new item's dV / dK start from zero: the previous item's must have been read out of tensor memory
+          if (it == 0 && k > 0) mbar_wait(bAccFree, (k - 1) & 1);
+          tc_fence_after();
+          TRACE(5, it * 4 + 2);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {  // contraction over the 128 query rows, 16 per step
-          // A = P^T (MN-major view of P[q][key]: two 64-key atoms 16 KB apart); B = dO (MN-major)
-          const uint64_t da = umma_smem_desc(sPb + k * 2048, kTileBytes, 1024);
-          const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss_p(tdV, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u, lead);
-        }
-        tc_commit_p(bPfree, lead);  // P may be overwritten while dK and dQ are still being computed
+          for (int kk = 0; kk < 8; ++kk) {  // contraction over the 128 query rows, 16 per step
+            // A = P^T (MN-major view of P[q][key]: two 64-key atoms 16 KB apart); B = dO (MN-major)
+            const uint64_t da = umma_smem_desc(sP + kk * 2048, kTileBytes, 1024);
+            const uint64_t db = umma_smem_desc(sdO + stage * kTileBytes + kk * 2048, kTileBytes, 1024);
+            umma_bf16_ss_p(tdV, da, db, idesc_kv, (it > 0 || kk > 0) ? 1u : 0u, lead);
+          }
+          tc_commit_p(bPfree, lead);  // P may be overwritten while dK and dQ are still being computed
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint64_t da = umma_smem_desc(sdSb + k * 2048, kTileBytes, 1024);
-          const uint64_t db = umma_smem_desc(sQ + stage * kTileBytes + k * 2048, kTileBytes, 1024);
-          umma_bf16_ss_p(tdK, da, db, idesc_kv, (it > 0 || k > 0) ? 1u : 0u, lead);
-        }
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint64_t da = umma_smem_desc(sdS + kk * 2048, kTileBytes, 1024);
+            const uint64_t db = umma_smem_desc(sQ + stage * kTileBytes + kk * 2048, kTileBytes, 1024);
+            umma_bf16_ss_p(tdK, da, db, idesc_kv, (it > 0 || kk > 0) ? 1u : 0u, lead);
+          }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {  // contraction over the 128 keys
-          const uint64_t db = umma_smem_desc(sK + k * 2048, kTileBytes, 1024);
-          umma_bf16_ts_p(tdQ, tdS + k * 8, db, idesc_dq, k > 0 ? 1u : 0u, lead);
+          for (int kk = 0; kk < 8; ++kk) {  // contraction over the 128 keys
+            const uint64_t db = umma_smem_desc(sK + kk * 2048, kTileBytes, 1024);
+            umma_bf16_ts_p(tdQ, tdS + kk * 8, db, idesc_dq, kk > 0 ? 1u : 0u, lead);
+          }
+          tc_commit_p(bdQfull, lead);
+          tc_commit_p(bStageEmpty(stage), lead);
+          TRACE(5, it * 4 + 3);
         }
-        tc_commit_p(bdQfull, lead);
-        tc_commit_p(bStageEmpty(stage), lead);
-        TRACE(5, it * 4 + 3);
+        tc_commit_p(bAccFull, lead);
+        ring += w.n_it + 1;  // (+1: the rotation-table turn of the ring)
+        if (!next_item(k + 1, w)) break;
       }
-      tc_commit_p(bAccFull, lead);
     }
     __syncwarp();
   } else if (warp >= 8 && warp < 12) {
     // ============================== dQ warpgroup (128 threads: one dQ row each) ==============================
-    // dQ of query tile (i_lo + it): TMEM -> fp32 staging tile in shared memory -> one TMA reduce-add per 32-column
-    // half into dq_acc (fp32, L2-side add).  Runs beside the compute warpgroups, off their critical path.
+    // dQ of every tile: TMEM -> fp32 staging tile in shared memory -> one TMA reduce-add per 32-column half into
+    // dq_acc (fp32, L2-side add).  Runs beside the compute warpgroups, off their critical path.
     reg_dealloc<96>();
     const int r = tid & 127;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t stage_base = sbase + AttnBwdSmem::kdQ;
-    for (int it = 0; it < n_it; ++it) {
-      mbar_wait(bdQfull, it & 1);
-      tc_fence_after();
-      uint32_t q0r[32], q1r[32];
-      tmem_ld_32x32b_x32(tdQ + lane_off, q0r);
-      tmem_ld_32x32b_x32(tdQ + lane_off + 32, q1r);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(bdQempty);
-      if (r == 0) tma_store_wait_read<0>();  // the previous reduce-add has finished reading the staging tile
-      named_bar_sync(1, 128);
-      const uint32_t srow = stage_base + r * 128;
+    Item w = first;
+    int g = 0;
+    for (int k = 0;; ++k) {
+      for (int it = 0; it < w.n_it; ++it, ++g) {
+        mbar_wait(bdQfull, g & 1);
+        tc_fence_after();
+        uint32_t q0r[32], q1r[32];
+        tmem_ld_32x32b_x32(tdQ + lane_off, q0r);
+        tmem_ld_32x32b_x32(tdQ + lane_off + 32, q1r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(bdQempty);
+        if (r == 0) tma_store_wait_read<0>();  // the previous reduce-add has finished reading the staging tile
+        named_bar_sync(1, 128);
+        const uint32_t srow = stage_base + r * 128;
 #pragma unroll
-      for (int v = 0; v < 8; ++v) {
-        st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(q0r[v * 4], q0r[v * 4 + 1], q0r[v * 4 + 2], q0r[v * 4 + 3]));
-        st_shared_v4(srow + kTileBytes + ((v ^ (r & 7)) << 4),
-                     make_uint4(q1r[v * 4], q1r[v * 4 + 1], q1r[v * 4 + 2], q1r[v * 4 + 3]));
+        for (int v = 0; v < 8; ++v) {
+          st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(q0r[v * 4], q0r[v * 4 + 1], q0r[v * 4 + 2], q0r[v * 4 + 3]));
+          st_shared_v4(srow + kTileBytes + ((v ^ (r & 7)) << 4),
+                       make_uint4(q1r[v * 4], q1r[v * 4 + 1], q1r[v * 4 + 2], q1r[v * 4 + 3]));
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (r == 0) {
+          const int row0 = static_cast<int>(w.seq_row0) + (w.i_lo + it) * 128;
+          tma_reduce_add_2d(&tm_dq, stage_base, w.h * 64, row0);
+          tma_reduce_add_2d(&tm_dq, stage_base + kTileBytes, w.h * 64 + 32, row0);
+          tma_store_commit();
+        }
       }
-      fence_proxy_async_smem();
-      named_bar_sync(1, 128);
-      if (r == 0) {
-        const int row0 = static_cast<int>(seq_row0) + (i_lo + it) * 128;
-        tma_reduce_add_2d(&tm_dq, stage_base, h * 64, row0);
-        tma_reduce_add_2d(&tm_dq, stage_base + kTileBytes, h * 64 + 32, row0);
-        tma_store_commit();
-      }
+      if (!next_item(k + 1, w)) break;
     }
     TRACE(7, 0);
     if (r == 0) tma_store_wait<0>();
@@ -825,139 +898,159 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const int half = tid >> 7;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     constexpr float c2 = kSoftmaxScale * kLog2e;
-    // per-row statistics of a query tile; those of tile it + 1 are requested while tile it is being worked on, so
-    // their global-memory latency stays off the loop's critical path
-    float n_lse = 0.f, n_dlt = 0.f;
-    int n_ds = 0, n_dshi = 0;
-    auto load_stats = [&](int it) {
-      const int i = i_lo + it;
-      const int t = min(i * 128 + r, T - 1);
-      const long stat_idx = (static_cast<long>(b) * NH + h) * T + t;
-      n_lse = __ldg(lse + stat_idx);
-      n_dlt = __ldg(delta + stat_idx);
-      if (doc_start) {
-        n_ds = __ldg(doc_start + seq_row0 + t);
-        n_dshi = __ldg(doc_start + seq_row0 + min(i * 128 + 127, T - 1));
-      }
-    };
-    if (n_it > 0) load_stats(0);
-    for (int it = 0; it < n_it; ++it) {
-      const int i = i_lo + it;
-      const int t = i * 128 + r;
-      const float lse2 = n_lse * kLog2e;
-      const float dlt_s = n_dlt * kSoftmaxScale;
-      const int ds_t = n_ds;
-      const int ds_hi_of_tile = n_dshi;
-      const bool need_mask = (key0 + 127 > i * 128) || (key0 < ds_hi_of_tile);
-      TRACE(half, it * 4 + 0);
-      mbar_wait(bSdPfull, it & 1);
-      tc_fence_after();
-      if (it + 1 < n_it) load_stats(it + 1);
-      TRACE(half, it * 4 + 1);
-      // the math for this thread's 64 columns stays in registers ...
-      uint32_t pk_p[2][16], pk_ds[2][16];
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        const int col0 = half * 64 + c * 32;
-        uint32_t sr[32], pr[32];
-        tmem_ld_32x32b_x32(tS + lane_off + col0, sr);
-        tmem_ld_32x32b_x32(tdP + lane_off + col0, pr);
-        tmem_ld_wait();
-        if (c == 1) {  // this thread's share of S and dP has left tensor memory
-          tc_fence_before();
-          mbar_arrive(bSdPfree);
+    Item w = first;
+    int g = 0, ring = 0;
+    for (int k = 0;; ++k) {
+      const int b = w.b, h = w.h, i_lo = w.i_lo, n_it = w.n_it, key0 = w.key0;
+      const long seq_row0 = w.seq_row0;
+      // per-row statistics of a query tile; those of tile it + 1 are requested while tile it is being worked on, so
+      // their global-memory latency stays off the loop's critical path
+      float n_lse = 0.f, n_dlt = 0.f;
+      int n_ds = 0, n_dshi = 0;
+      auto load_stats = [&](int it) {
+        const int i = i_lo + it;
+        const int t = min(i * 128 + r, T - 1);
+        const long stat_idx = (static_cast<long>(b) * NH + h) * T + t;
+        n_lse = __ldg(lse + stat_idx);
+        n_dlt = __ldg(delta + stat_idx);
+        if (doc_start) {
+          n_ds = __ldg(doc_start + seq_row0 + t);
+          n_dshi = __ldg(doc_start + seq_row0 + min(i * 128 + 127, T - 1));
         }
-        if (need_mask) chunk_p_ds<true>(sr, pr, c2, lse2, dlt_s, ds_t - key0 - col0, t - key0 - col0, pk_p[c], pk_ds[c]);
-        else chunk_p_ds<false>(sr, pr, c2, lse2, dlt_s, 0, 0, pk_p[c], pk_ds[c]);
-        // P leaves for shared memory chunk by chunk, under the math of the next chunk: its buffer is free as soon as
-        // the previous tile's dV MMAs are done (dS has to wait for dK and dQ as well)
-        if (c == 0 && it > 0) mbar_wait(bPfree, (it - 1) & 1);
+      };
+      load_stats(0);
+      for (int it = 0; it < n_it; ++it, ++g) {
+        const int i = i_lo + it;
+        const int t = i * 128 + r;
+        const float lse2 = n_lse * kLog2e;
+        const float dlt_s = n_dlt * kSoftmaxScale;
+        const int ds_t = n_ds;
+        const int ds_hi_of_tile = n_dshi;
+        const bool need_mask = (key0 + 127 > i * 128) || (key0 < ds_hi_of_tile);
+        TRACE(half, it * 4 + 0);
+        mbar_wait(bSdPfull, g & 1);
+        tc_fence_after();
+        if (it + 1 < n_it) load_stats(it + 1);
+        TRACE(half, it * 4 + 1);
+        // the math for this thread's 64 columns stays in registers ...
+        uint32_t pk_p[2][16], pk_ds[2][16];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int col0 = half * 64 + c * 32;
+          uint32_t sr[32], pr[32];
+          tmem_ld_32x32b_x32(tS + lane_off + col0, sr);
+          tmem_ld_32x32b_x32(tdP + lane_off + col0, pr);
+          tmem_ld_wait();
+          if (c == 1) {  // this thread's share of S and dP has left tensor memory
+            tc_fence_before();
+            mbar_arrive(bSdPfree);
+          }
+          if (need_mask) chunk_p_ds<true>(sr, pr, c2, lse2, dlt_s, ds_t - key0 - col0, t - key0 - col0, pk_p[c], pk_ds[c]);
+          else chunk_p_ds<false>(sr, pr, c2, lse2, dlt_s, 0, 0, pk_p[c], pk_ds[c]);
+          // P leaves for shared memory chunk by chunk, under the math of the next chunk: its buffer is free as soon as
+          // the previous tile's dV MMAs are done (dS has to wait for dK and dQ as well) and, at the start of an item,
+          // once the previous item's dK / dV stores have read it
+          if (c == 0) {
+            if (g > 0) mbar_wait(bPfree, (g - 1) & 1);
+            if (it == 0 && k > 0) mbar_wait(bStaged, (k - 1) & 1);
+          }
+          {
+            const uint32_t rowoff = half * kTileBytes + r * 128;
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
+              st_shared_v4(sP + off, make_uint4(pk_p[c][v * 4], pk_p[c][v * 4 + 1], pk_p[c][v * 4 + 2], pk_p[c][v * 4 + 3]));
+            }
+          }
+        }
+        // ... until the previous tile's dV/dK/dQ MMAs (which read P and dS from shared memory) have completed
+        TRACE(half, it * 4 + 2);
+        if (g > 0) mbar_wait(bdQfull, (g - 1) & 1);
+        TRACE(half, it * 4 + 3);
         {
           const uint32_t rowoff = half * kTileBytes + r * 128;
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
-            st_shared_v4(sP + off, make_uint4(pk_p[c][v * 4], pk_p[c][v * 4 + 1], pk_p[c][v * 4 + 2], pk_p[c][v * 4 + 3]));
-          }
+          for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
+              st_shared_v4(sdS + off, make_uint4(pk_ds[c][v * 4], pk_ds[c][v * 4 + 1], pk_ds[c][v * 4 + 2], pk_ds[c][v * 4 + 3]));
+            }
         }
+        TRACE(2 + half, it * 4 + 0);
+        // dS a second time, into tensor memory (32 columns of bf16 pairs per thread), for dQ = dS.K
+        tmem_st_32x32b_x16(tdS + lane_off + half * 32, pk_ds[0]);
+        tmem_st_32x32b_x16(tdS + lane_off + half * 32 + 16, pk_ds[1]);
+        tmem_st_wait();
+        TRACE(2 + half, it * 4 + 1);
+        tc_fence_before();
+        fence_proxy_async_smem();
+        TRACE(2 + half, it * 4 + 2);
+        mbar_arrive(bPdSfull);
+        TRACE(2 + half, it * 4 + 3);
       }
-      // ... until the previous tile's dV/dK/dQ MMAs (which read P and dS from shared memory) have completed
-      TRACE(half, it * 4 + 2);
-      if (it > 0) mbar_wait(bdQfull, (it - 1) & 1);
-      TRACE(half, it * 4 + 3);
+      // ---- the item's dK / dV (the next item's loads and first S / dP MMAs are already on their way)
+      TRACE(6, 0);
       {
-        const uint32_t rowoff = half * kTileBytes + r * 128;
+        const int cs_stage = (ring + n_it) % kStages;
+        mbar_wait(bAccFull, k & 1);
+        tc_fence_after();
+        TRACE(6, 1);
+        // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
+        uint32_t kr[32], vr[32];
+        tmem_ld_32x32b_x32(tdK + lane_off + half * 32, kr);
+        tmem_ld_32x32b_x32(tdV + lane_off + half * 32, vr);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(bAccFree);  // the next item's dV / dK MMAs may overwrite the accumulators
+        TRACE(6, 6);
+        // (cos, sin) of this key row: in the ring slot after the last Q / dO tile, 128B-swizzled rows of 32 floats
+        mbar_wait(bQdOfull(cs_stage), ((ring + n_it) / kStages) & 1);
+        const uint32_t cs_row = (half == 0 ? sQ : sdO) + cs_stage * kTileBytes + r * 128;
+        // dV and dK (un-rotated) leave as two 128 x 64 bf16 tiles through the P buffer and one TMA store each
+        const uint32_t out_row = sP + r * 128;
 #pragma unroll
-        for (int c = 0; c < 2; ++c)
-#pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            const uint32_t off = rowoff + (((c * 4 + v) ^ (r & 7)) << 4);
-            st_shared_v4(sdS + off, make_uint4(pk_ds[c][v * 4], pk_ds[c][v * 4 + 1], pk_ds[c][v * 4 + 2], pk_ds[c][v * 4 + 3]));
-          }
+        for (int v = 0; v < 4; ++v) {
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(vr[v * 8 + 0]), __uint_as_float(vr[v * 8 + 1]));
+          o.y = pack_bf16x2(__uint_as_float(vr[v * 8 + 2]), __uint_as_float(vr[v * 8 + 3]));
+          o.z = pack_bf16x2(__uint_as_float(vr[v * 8 + 4]), __uint_as_float(vr[v * 8 + 5]));
+          o.w = pack_bf16x2(__uint_as_float(vr[v * 8 + 6]), __uint_as_float(vr[v * 8 + 7]));
+          st_shared_v4(out_row + (((half * 4 + v) ^ (r & 7)) << 4), o);
+          // dK: transpose of the rotation, applied to the fp32 accumulators
+          const uint4 u0 = ld_shared_v4(cs_row + (((2 * v) ^ (r & 7)) << 4));
+          const uint4 u1 = ld_shared_v4(cs_row + (((2 * v + 1) ^ (r & 7)) << 4));
+          const float4 c0 = make_float4(__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w));
+          const float4 c1 = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w));
+          const float g0 = __uint_as_float(kr[v * 8 + 0]), g1 = __uint_as_float(kr[v * 8 + 1]);
+          const float g2 = __uint_as_float(kr[v * 8 + 2]), g3 = __uint_as_float(kr[v * 8 + 3]);
+          const float g4 = __uint_as_float(kr[v * 8 + 4]), g5 = __uint_as_float(kr[v * 8 + 5]);
+          const float g6 = __uint_as_float(kr[v * 8 + 6]), g7 = __uint_as_float(kr[v * 8 + 7]);
+          uint4 q;
+          q.x = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
+          q.y = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
+          q.z = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
+          q.w = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
+          st_shared_v4(out_row + kTileBytes + (((half * 4 + v) ^ (r & 7)) << 4), q);
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(2, 256);
+        if (tid == 0) {
+          mbar_arrive(bStageEmpty(cs_stage));  // every thread has read its rotation-table row: the ring slot is free
+          const int row0 = static_cast<int>(seq_row0) + key0;
+          tma_store_2d(&tm_dqkv, sP, 2 * d + h * 64, row0);
+          tma_store_2d(&tm_dqkv, sP + kTileBytes, d + h * 64, row0);
+          tma_store_commit();
+          tma_store_wait_read<0>();  // the P buffer may be written again (and shared memory given up at the end)
+          mbar_arrive(bStaged);
+        }
+        TRACE(6, 2);
       }
-      TRACE(2 + half, it * 4 + 0);
-      // dS a second time, into tensor memory (32 columns of bf16 pairs per thread), for dQ = dS.K
-      tmem_st_32x32b_x16(tdS + lane_off + half * 32, pk_ds[0]);
-      tmem_st_32x32b_x16(tdS + lane_off + half * 32 + 16, pk_ds[1]);
-      tmem_st_wait();
-      TRACE(2 + half, it * 4 + 1);
-      tc_fence_before();
-      fence_proxy_async_smem();
-      TRACE(2 + half, it * 4 + 2);
-      mbar_arrive(bPdSfull);
-      TRACE(2 + half, it * 4 + 3);
-    }
-    // ---- tail: dK / dV
-    TRACE(6, 0);
-    if (n_it > 0) {
-      mbar_wait(bAccFull, 0);
-      tc_fence_after();
-      TRACE(6, 1);
-      // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
-      uint32_t kr[32], vr[32];
-      tmem_ld_32x32b_x32(tdK + lane_off + half * 32, kr);
-      tmem_ld_32x32b_x32(tdV + lane_off + half * 32, vr);
-      tmem_ld_wait();
-      TRACE(6, 6);
-      // (cos, sin) of this key row: in the ring slot after the last Q / dO tile, 128B-swizzled rows of 32 floats
-      mbar_wait(bCSfull, 0);
-      const uint32_t cs_row = (half == 0 ? sQ : sdO) + (n_it % 3) * kTileBytes + r * 128;
-      // dV and dK (un-rotated) leave as two 128 x 64 bf16 tiles through the P buffer and one TMA store each
-      const uint32_t out_row = sP + r * 128;
-#pragma unroll
-      for (int v = 0; v < 4; ++v) {
-        uint4 o;
-        o.x = pack_bf16x2(__uint_as_float(vr[v * 8 + 0]), __uint_as_float(vr[v * 8 + 1]));
-        o.y = pack_bf16x2(__uint_as_float(vr[v * 8 + 2]), __uint_as_float(vr[v * 8 + 3]));
-        o.z = pack_bf16x2(__uint_as_float(vr[v * 8 + 4]), __uint_as_float(vr[v * 8 + 5]));
-        o.w = pack_bf16x2(__uint_as_float(vr[v * 8 + 6]), __uint_as_float(vr[v * 8 + 7]));
-        st_shared_v4(out_row + (((half * 4 + v) ^ (r & 7)) << 4), o);
-        // dK: transpose of the rotation, applied to the fp32 accumulators
-        const uint4 u0 = ld_shared_v4(cs_row + (((2 * v) ^ (r & 7)) << 4));
-        const uint4 u1 = ld_shared_v4(cs_row + (((2 * v + 1) ^ (r & 7)) << 4));
-        const float4 c0 = make_float4(__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w));
-        const float4 c1 = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w));
-        const float g0 = __uint_as_float(kr[v * 8 + 0]), g1 = __uint_as_float(kr[v * 8 + 1]);
-        const float g2 = __uint_as_float(kr[v * 8 + 2]), g3 = __uint_as_float(kr[v * 8 + 3]);
-        const float g4 = __uint_as_float(kr[v * 8 + 4]), g5 = __uint_as_float(kr[v * 8 + 5]);
-        const float g6 = __uint_as_float(kr[v * 8 + 6]), g7 = __uint_as_float(kr[v * 8 + 7]);
-        uint4 q;
-        q.x = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
-        q.y = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
-        q.z = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
-        q.w = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
-        st_shared_v4(out_row + kTileBytes + (((half * 4 + v) ^ (r & 7)) << 4), q);
-      }
-      fence_proxy_async_smem();
-      named_bar_sync(2, 256);
-      if (tid == 0) {
-        const int row0 = static_cast<int>(seq_row0) + key0;
-        tma_store_2d(&tm_dqkv, sP, 2 * d + h * 64, row0);
-        tma_store_2d(&tm_dqkv, sP + kTileBytes, d + h * 64, row0);
-        tma_store_commit();
-        tma_store_wait_read<0>();  // shared memory is given up when the CTA exits
-      }
-      TRACE(6, 2);
+      ring += n_it + 1;
+#ifdef PCV_TRACE
+      ++trace_items;
+#endif
+      if (!next_item(k + 1, w)) break;
     }
   }
   tc_fence_before();
@@ -971,7 +1064,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   TRACE(6, 4);
   if (tid == 0 && cta_lin < 4096) {
     g_cta_trace[cta_lin * 4 + 1] = gtimer();
-    g_cta_trace[cta_lin * 4 + 3] = n_it;
+    g_cta_trace[cta_lin * 4 + 3] = trace_items;
   }
 #endif
 }
@@ -1031,6 +1124,11 @@ static int attn_check(int B, int T, int NH) {
 #ifdef PCV_TRACE
 extern "C" int pcv_debug_read_trace(long long* host, int n) {
   return static_cast<int>(cudaMemcpyFromSymbol(host, pcv::g_trace, sizeof(long long) * n));
+}
+extern "C" int pcv_debug_clear_cta_trace(void) {
+  void* p = nullptr;
+  cudaGetSymbolAddress(&p, pcv::g_cta_trace);
+  return static_cast<int>(cudaMemset(p, 0, sizeof(long long) * 4096 * 4));
 }
 extern "C" int pcv_debug_read_cta_trace(long long* host, int n) {
   return static_cast<int>(cudaMemcpyFromSymbol(host, pcv::g_cta_trace, sizeof(long long) * n));

@@ -8,6 +8,9 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 
+#ifdef PCV_HANG_DEBUG
+#include <cstdio>
+#endif
 namespace pcv {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -40,9 +43,56 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return done != 0;
 }
+#ifdef PCV_HANG_DEBUG
+// Debug builds only (-DPCV_HANG_DEBUG): a wait that has spun for ~0.2 s reports who waits on which barrier (byte offset
+// inside the 1 KB-aligned barrier block) and traps, instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  bool said = false;
+  while (!mbar_try_wait(bar, parity)) {
+    const long long dt = clock64() - t0;
+    if (dt > 200000000LL && !said) {
+      said = true;
+      if ((threadIdx.x & 31) == 0 || threadIdx.x == 0)
+        printf("HANG block (%d,%d,%d) thread %d: barrier index %u parity %u\n", blockIdx.x, blockIdx.y, blockIdx.z,
+               threadIdx.x, (bar & 1023u) >> 3, parity);
+    }
+    if (dt > 600000000LL) __trap();
+  }
+}
+#else
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
+}
+#endif
+
+// ------------------------------------------------------------------ cluster launch control (work stealing)
+// A running CTA asks the hardware to cancel the launch of a CTA of the same grid that has not started yet and, if that
+// succeeds, works on the cancelled CTA's blockIdx itself: a persistent kernel with the launch order of the grid as its
+// (dynamic) work queue and no counter in global memory.  The 16-byte answer lands in shared memory and completes 16
+// transaction bytes on `bar`.  After a failed attempt (nothing left to cancel) no further attempt may be made.
+__device__ __forceinline__ void clc_try_cancel(uint32_t result_smem, uint32_t bar) {
+  asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
+               ::"r"(result_smem), "r"(bar) : "memory");
+}
+// -> true and the cancelled CTA's blockIdx if the attempt answered in `result_smem` succeeded
+__device__ __forceinline__ bool clc_query(uint32_t result_smem, int& x, int& y, int& z) {
+  uint32_t ok, bx = 0, by = 0, bz = 0;
+  asm volatile(
+      "{\n"
+      ".reg .pred p1;\n"
+      ".reg .b128 r;\n"
+      "ld.shared.b128 r, [%4];\n"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n"
+      "selp.u32 %3, 1, 0, p1;\n"
+      "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%0, %1, %2, _}, r;\n"
+      "}\n"
+      : "+r"(bx), "+r"(by), "+r"(bz), "=r"(ok)
+      : "r"(result_smem)
+      : "memory");
+  x = static_cast<int>(bx); y = static_cast<int>(by); z = static_cast<int>(bz);
+  return ok != 0;
 }
 
 // generic-proxy writes to smem -> visible to the async proxy (TMA / tcgen05 operand reads)

@@ -21,6 +21,7 @@ def cta_report(tag, n_cta):
     lib.pcv_debug_read_cta_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
     lib.pcv_debug_read_cta_trace(cbuf, 4096 * 4)
     c = np.array(cbuf[:], dtype=np.int64).reshape(4096, 4)[:n_cta]
+    c = c[(c[:, 0] > 0) & (c[:, 1] > c[:, 0])]  # persistent kernels: CTAs whose launch was cancelled never ran
     t_begin, t_end = c[:, 0].min(), c[:, 1].max()
     print(f"--- {tag} CTA occupancy: kernel span {(t_end - t_begin) / 1e3:.1f} us, {len(c)} CTAs on {len(set(c[:, 2]))} SMs")
     busy = (c[:, 1] - c[:, 0]).sum() / 1e3
@@ -63,8 +64,10 @@ cta_report('fwd', B * NH * (T // 128))
 
 # ---- backward
 dout = torch.randn(B * T, d, device="cuda").to(torch.bfloat16)
-for _ in range(2):
-    ops.attn_bwd(qkv, cs, None, out, dout, lse, B, T, NH)
+ops.attn_bwd(qkv, cs, None, out, dout, lse, B, T, NH)
+torch.cuda.synchronize()
+lib.pcv_debug_clear_cta_trace()  # persistent kernel: CTAs whose launch is cancelled leave no record
+ops.attn_bwd(qkv, cs, None, out, dout, lse, B, T, NH)
 torch.cuda.synchronize()
 lib.pcv_debug_read_trace(buf, 8192)
 a = np.array(buf[:], dtype=np.int64).reshape(8, 1024)
