@@ -1,30 +1,33 @@
 // attention.cu — flash-style causal / document-masked attention forward and backward on tcgen05 + TMEM for sm_100a,
-// head_dim = 64, with the interleaved-pair RoPE of the reference fused into the Q/K tile load.
+// head_dim = 64.  q and k arrive ALREADY ROTATED: the interleaved-pair RoPE of the reference is applied by the QKV GEMM
+// epilogue (pcv_gemm_bf16_rope) or by pcv_rope_qk below; the backward kernels apply its transpose to dQ and dK.
 //
 // Replaces, on the reference's hot path (all XLA-generated there, O(T^2) memory):
-//   apply_rotary_emb_complex_like      models/LM/embedding.py:28-67   (call: models/LM/transformer.py:212)
 //   jax.nn.dot_product_attention       models/LM/transformer.py:233-240  (fp32 logits/softmax, bf16 P before P.V)
 //   the bool [B,T,T] block-diagonal mask of train_lm.py:107-131 / data_prep_utils.py:14-43 — consumed here as
 //   doc_start[b*T+t] (first position of t's document); the [T,T] mask is never built.
+//   apply_rotary_emb_complex_like      models/LM/embedding.py:28-67  (stand-alone form: rope_qk_kernel)
 // and their autodiff transposes (train_lm.py:267).
 //
 // Layout: qkv[B*T][3d] bf16, columns [q | k | v], each third head-major [N][64].  out[B*T][d] bf16.
-// lse[B][N][T] fp32 (natural log).  Tiles are 128 rows x 64 columns = 128 x 128 B, 128B-swizzled in shared memory:
-// K-major operand for Q.K^T, and the *same bytes* serve as the MN-major operand of P.V / dS^T.Q / P^T.dO.
+// lse[B][N][T] fp32 (natural log).  Tiles are 128 rows x 64 columns = 128 x 128 B, loaded by TMA and 128B-swizzled in
+// shared memory: K-major operand for Q.K^T, and the *same bytes* serve as the MN-major operand of P.V / dS^T.Q / P^T.dO.
 //
-// Forward CTA (416 threads) = one (batch, head, 256-query block):
-//   warps 0-3 / 4-7 : softmax warpgroup 0 / 1, one thread per query row of its 128-row tile; S read from TMEM in two
-//                     passes (row max, then exp2 + bf16 P into shared memory); the running output is kept in registers
-//                     and folded with the per-tile P.V read back from TMEM one tile late (so it overlaps the MMAs)
-//   warps 8-11      : loader — global -> RoPE in registers -> swizzled shared memory for Q and K; TMA for V
-//   warp 12         : tcgen05.mma issuer (one lane): S_w = Q_w.K_j^T, O_w,j = P_w.V_j, ping-ponged between the two
-//                     warpgroups so one group's MMAs run under the other's exponentials
-// TMEM (512 columns): S0 [0,128) S1 [128,256) O0 {[256,320),[320,384)} O1 {[384,448),[448,512)}.
+// Forward (attn_fwd_kernel, 192 threads, TWO CTAs per SM): one CTA = one (batch, head, 128-query tile).
+//   warps 0-3 : softmax warpgroup, one thread per query row; 64-key half tiles, S double-buffered in tensor memory, one
+//               pass per half tile with a lazily moved exponent reference; P goes back to tensor memory as bf16
+//   warp 4    : TMA producer (Q; K / V rings of 2) + tensor-memory allocation;   warp 5 : tcgen05.mma issuer
+//   TMEM (256 columns per CTA): S0 [0,64) S1 [64,128) O [128,192) P0 [192,224) P1 [224,256).
 //
-// Backward CTA (416 threads) = one (batch, head, 128-key tile), looping over the query tiles that can see it:
-//   S = Q_i.K^T, dP = dO_i.V^T  ->  P = exp2(S*c - lse), dS = P*(dP - delta)*scale (256 threads, half a row each)
-//   dV += P^T.dO_i, dK += dS^T.Q_i (accumulated in TMEM over the loop), dQ_i = dS.K (read back, red.add into fp32 dq)
-// TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448) dS(bf16 pairs) [448,512).
+// Backward (attn_bwd_kernel, 512 threads, persistent): a CTA takes (batch, head, 128-key tile) items — its own
+// blockIdx first, then launches it cancels through cluster launch control — and loops over the query tiles that see
+// the key tile:  S = Q_i.K^T, dP = dO_i.V^T -> P = exp2(S*c - lse), dS = P*(dP - delta)*scale;
+//   dV += P^T.dO_i, dK += dS^T.Q_i (accumulated in tensor memory over the loop), dQ_i = dS.K (TMA reduce-add into fp32).
+//   warps 0-7 : compute (row r, 64 key columns each);  warps 8-11 : everything that leaves tensor memory (dQ per tile,
+//   dK / dV per item);  warp 12 : TMA producer + work stealing;  warp 13 : tcgen05.mma issuer
+//   TMEM: S [0,128) dP [128,256) dV [256,320) dK [320,384) dQ [384,448) dS(bf16 pairs) [448,512).
+// attn_bwd_prep_kernel (delta = rowsum(dO * O), zero-fill of the dQ accumulator) runs before it,
+// attn_bwd_dq_post_kernel (un-rotation + bf16 of dQ) after it.
 #include "sm100.cuh"
 #include "pcv_internal.h"
 #include <math.h>
@@ -526,8 +529,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
 // ================================================================================================ backward
 // delta[b][h][t] = sum_c dout[b,t,h,c] * out[b,t,h,c]   (one warp per (token, head) pair would waste lanes: 8 lanes each)
+// and, in the same pass over [B*T][d], the zero-fill of the fp32 dQ accumulator the main kernel reduce-adds into (a
+// separate 64 MB memset node per layer cost 20 us at the 420M shape; here its stores ride under the loads).
 __global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
-                                     float* __restrict__ delta, int BT, int T, int NH) {
+                                     float* __restrict__ delta, float* __restrict__ dq_acc, int BT, int T, int NH) {
   const long gid = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
   const long item = gid >> 3;  // (row, head)
   const int c = static_cast<int>(gid & 7);
@@ -536,6 +541,8 @@ __global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ out, cons
   const int h = static_cast<int>(item % NH);
   const long off = row * (NH * 64) + h * 64 + c * 8;
   const uint4 a = ld_global_nc_v4(out + off), g = ld_global_nc_v4(dout + off);
+  *reinterpret_cast<float4*>(dq_acc + off) = make_float4(0.f, 0.f, 0.f, 0.f);
+  *reinterpret_cast<float4*>(dq_acc + off + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
   const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
   float s = 0.f;
 #pragma unroll
@@ -554,16 +561,16 @@ __global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ out, cons
 }
 
 struct AttnBwdSmem {
-  static constexpr int kK = 0;                      // K_j rotated
-  static constexpr int kV = kK + kTileBytes;        // V_j
+  static constexpr int kK = 0;                      // 2 buffers: K_j rotated, of this item and (prefetched) of the next
+  static constexpr int kV = kK + 2 * kTileBytes;    // V_j
   static constexpr int kStages = 3;                 // Q_i / dO_i ring
   static constexpr int kQ = kV + kTileBytes;        // kStages x rotated Q_i
   static constexpr int kdO = kQ + kStages * kTileBytes;
   static constexpr int kP = kdO + kStages * kTileBytes;  // 128 x 128 bf16
   static constexpr int kdS = kP + 2 * kTileBytes;   // 128 x 128 bf16
-  static constexpr int kdQ = kdS + 2 * kTileBytes;  // fp32 staging of dQ: 2 halves x (128 rows x 32 columns)
-  static constexpr int kBar = kdQ + 2 * kTileBytes;
-  static constexpr int kBytes = kBar + 256 + 1024;
+  static constexpr int kOut = kdS + 2 * kTileBytes;  // one staging tile of the dQ warpgroup: fp32 128 x 32 or bf16 128 x 64
+  static constexpr int kBar = kOut + kTileBytes;    // 256 bytes of barriers, 64 of work-stealing answers
+  static constexpr int kBytes = kBar + 512 + 1024;
 };
 static_assert(AttnBwdSmem::kBytes <= 232448, "attn_bwd shared memory");
 
@@ -598,12 +605,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   constexpr int kStages = AttnBwdSmem::kStages;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sK = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV, sQ = sbase + AttnBwdSmem::kQ,
+  const uint32_t sK0 = sbase + AttnBwdSmem::kK, sV = sbase + AttnBwdSmem::kV, sQ = sbase + AttnBwdSmem::kQ,
                  sdO = sbase + AttnBwdSmem::kdO, sP = sbase + AttnBwdSmem::kP, sdS = sbase + AttnBwdSmem::kdS,
-                 sBar = sbase + AttnBwdSmem::kBar;
-  const uint32_t bKVfull = sBar;                                  // (tx: K and V)                      per item
+                 sOut = sbase + AttnBwdSmem::kOut, sBar = sbase + AttnBwdSmem::kBar;
+  const uint32_t bVfull = sBar;                                   // (tx: V)                            per item
   auto bQdOfull = [&](int s) { return sBar + 8u * (1 + s); };     // [3] (tx: Q_i and dO_i)             per ring turn
-  auto bStageEmpty = [&](int s) { return sBar + 8u * (4 + s); };  // [3] (1: commit, or the tail's arrive)
+  auto bStageEmpty = [&](int s) { return sBar + 8u * (4 + s); };  // [3] (1: commit, or the dK/dV tail's arrive)
   const uint32_t bSdPfull = sBar + 8u * 8;                        // (1, commit)                        per tile
   const uint32_t bPdSfull = sBar + 8u * 9;                        // (256)                              per tile
   const uint32_t bdQfull = sBar + 8u * 10;                        // (1, commit)                        per tile
@@ -612,10 +619,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t tmem_ptr_smem = sBar + 8u * 13;
   const uint32_t bSdPfree = sBar + 8u * 14;                       // (256) S / dP of a tile are in registers
   const uint32_t bPfree = sBar + 8u * 15;                         // (1, commit) dV MMAs done: P in shared memory is free
-  const uint32_t bAccFree = sBar + 8u * 17;                       // (256) dK / dV have left tensor memory, per item
-  const uint32_t bStaged = sBar + 8u * 18;                        // (1) the dK / dV stores have read the P buffer, per item
-  auto bItem = [&](int u) { return sBar + 8u * (19 + u); };       // [2] (tx: 16 bytes) answer of the work-stealing request
-  auto sItem = [&](int u) { return sBar + 8u * 22 + 16u * u; };   // [2] x 16 bytes, 16-byte aligned
+  const uint32_t bVfree = sBar + 8u * 16;                         // (1, commit) the item's last dP MMA has read V
+  const uint32_t bAccFree = sBar + 8u * 17;                       // (128) dK / dV have left tensor memory, per item
+  auto bKfull = [&](int u) { return sBar + 8u * (18 + u); };      // [2] (tx: K) item k uses buffer k & 1
+  // answers of the work-stealing requests: item k' -> slot k' & 3.  Four slots, because the dQ warpgroup reads the answer
+  // for item k + 1 only after the dK / dV tail of item k, by when the producer may already have asked for item k + 3
+  auto bItem = [&](int u) { return sBar + 8u * (20 + u); };       // [4] (tx: 16 bytes)
+  auto bKfree = [&](int u) { return sBar + 8u * (24 + u); };      // [2] (1, commit) every MMA of the item on K buffer u is done
+  auto sItem = [&](int u) { return sBar + 256u + 16u * u; };      // [4] x 16 bytes, 16-byte aligned
   volatile uint32_t* tmem_ptr_generic = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -662,9 +673,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   };
   // item k + 1 of this CTA: the answer to the request issued while item k was loaded (every role reads it itself)
   auto next_item = [&](int k_next, Item& w) -> bool {
-    mbar_wait(bItem(k_next & 1), ((k_next - 1) >> 1) & 1);  // slot 1: items 1, 3, 5 ...; slot 0: items 2, 4, 6 ...
+    mbar_wait(bItem(k_next & 3), ((k_next - 1) >> 2) & 1);  // slot u: items u, u + 4, ... (item 0 is never asked for)
     int x, y, z;
-    if (!clc_query(sItem(k_next & 1), x, y, z)) return false;
+    if (!clc_query(sItem(k_next & 3), x, y, z)) return false;
     w = make_item(x, y, z);
     return true;
   };
@@ -676,7 +687,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tma_prefetch_desc(&tm_dq);
     tma_prefetch_desc(&tm_cs);
     tma_prefetch_desc(&tm_dqkv);
-    mbar_init(bKVfull, 1);
+    mbar_init(bVfull, 1);
+    mbar_init(bKfull(0), 1);
+    mbar_init(bKfull(1), 1);
+    mbar_init(bVfree, 1);
+    mbar_init(bKfree(0), 1);
+    mbar_init(bKfree(1), 1);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(bQdOfull(s), 1);
       mbar_init(bStageEmpty(s), 1);
@@ -688,17 +704,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(bdQfull, 1);
     mbar_init(bdQempty, 128);
     mbar_init(bAccFull, 1);
-    mbar_init(bAccFree, 256);
-    mbar_init(bStaged, 1);
-    mbar_init(bItem(0), 1);
-    mbar_init(bItem(1), 1);
+    mbar_init(bAccFree, 128);
+    for (int u = 0; u < 4; ++u) mbar_init(bItem(u), 1);
     fence_mbar_init();
     // K, V and the first Q / dO tile of the first item are requested right away: their latency runs under the
     // tensor-memory allocation and the block-wide barrier below
     const int row0 = static_cast<int>(first.seq_row0);
-    mbar_expect_tx(bKVfull, 2 * kTileBytes);
-    tma_load_2d(sK, &tm_qkv, bKVfull, d + first.h * 64, row0 + first.key0);
-    tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + first.h * 64, row0 + first.key0);
+    mbar_expect_tx(bKfull(0), kTileBytes);
+    tma_load_2d(sK0, &tm_qkv, bKfull(0), d + first.h * 64, row0 + first.key0);
+    mbar_expect_tx(bVfull, kTileBytes);
+    tma_load_2d(sV, &tm_qkv, bVfull, 2 * d + first.h * 64, row0 + first.key0);
     mbar_expect_tx(bQdOfull(0), 2 * kTileBytes);
     tma_load_2d(sQ, &tm_qkv, bQdOfull(0), first.h * 64, row0 + first.i_lo * 128);
     tma_load_2d(sdO, &tm_do, bQdOfull(0), first.h * 64, row0 + first.i_lo * 128);
@@ -715,7 +730,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                  tdS = tmem_base + 448;  // dS as bf16 pairs: the A operand of dQ = dS.K, read from tensor memory
 
   if (warp >= 12) {
-    reg_dealloc<56>();  // warpgroup 3: producer, MMA issuer, two idle warps (8 x 168 + 4 x 96 + 4 x 56 registers per lane: 62464 of 65536)
+    reg_dealloc<56>();  // warpgroup 3: producer, MMA issuer, two idle warps (8 x 160 + 4 x 120 + 4 x 56 registers per lane: 63488 of 65536)
   }
   if (warp == 12) {
     // ============================== TMA producer (q, k in qkv are already rotated) ==============================
@@ -725,15 +740,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       for (int k = 0;; ++k) {
         const int row0 = static_cast<int>(w.seq_row0);
         if (k > 0) {
-          // sK / sV are read by every MMA of the previous item: free once its last ones have completed
-          mbar_wait(bAccFull, (k - 1) & 1);
-          mbar_expect_tx(bKVfull, 2 * kTileBytes);
-          tma_load_2d(sK, &tm_qkv, bKVfull, d + w.h * 64, row0 + w.key0);
-          tma_load_2d(sV, &tm_qkv, bKVfull, 2 * d + w.h * 64, row0 + w.key0);
+          // This point is reached while the previous item still has ~3 tiles to go (the Q / dO ring holds the producer
+          // back), so both loads are prefetches.  K goes to the other K buffer, last read by item k - 2 ...
+          // (a barrier per buffer: its next phase cannot complete before this very load has landed)
+          if (k > 1) mbar_wait(bKfree(k & 1), ((k - 2) >> 1) & 1);
+          mbar_expect_tx(bKfull(k & 1), kTileBytes);
+          tma_load_2d(sK0 + (k & 1) * kTileBytes, &tm_qkv, bKfull(k & 1), d + w.h * 64, row0 + w.key0);
+          // ... V to the single V buffer as soon as the previous item's last dP MMA has read it
+          mbar_wait(bVfree, (k - 1) & 1);
+          mbar_expect_tx(bVfull, kTileBytes);
+          tma_load_2d(sV, &tm_qkv, bVfull, 2 * d + w.h * 64, row0 + w.key0);
         }
         // ask for the item after this one now: the answer is there long before it is needed
-        mbar_expect_tx(bItem((k + 1) & 1), 16);
-        clc_try_cancel(sItem((k + 1) & 1), bItem((k + 1) & 1));
+        mbar_expect_tx(bItem((k + 1) & 3), 16);
+        clc_try_cancel(sItem((k + 1) & 3), bItem((k + 1) & 3));
         for (int it = (k == 0 ? 1 : 0); it < w.n_it; ++it) {
           const int i = w.i_lo + it;
           const int rr = ring + it;
@@ -768,11 +788,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, false, false);   // S, dP
       constexpr uint32_t idesc_kv = umma_idesc_bf16(128, 64, true, true);     // dV = P^T.dO, dK = dS^T.Q
       constexpr uint32_t idesc_dq = umma_idesc_bf16(128, 64, false, true);    // dQ = dS.K
-      auto issue_SdP = [&](int stage) {
+      uint32_t sK = sK0;  // this item's K buffer
+      auto issue_SdP = [&](int stage, uint32_t k_buf) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) {
           const uint64_t da = umma_smem_desc(sQ + stage * kTileBytes + kk * 32, 16, 1024);
-          const uint64_t db = umma_smem_desc(sK + kk * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(k_buf + kk * 32, 16, 1024);
           umma_bf16_ss_p(tS, da, db, idesc_s, kk > 0 ? 1u : 0u, lead);
         }
 #pragma unroll
@@ -783,18 +804,24 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
         tc_commit_p(bSdPfull, lead);
       };
-      Item w = first;
+      Item w = first, wn = first;
+      bool first_issued = false;  // the item's first S / dP were already issued during the previous item's last tile
       int g = 0, ring = 0;
       for (int k = 0;; ++k) {
-        mbar_wait(bKVfull, k & 1);
-        {
+        sK = sK0 + (k & 1) * kTileBytes;
+        if (!first_issued) {
           // first S / dP of the item: its operands have landed and the previous tile's S / dP are in registers
+          mbar_wait(bKfull(k & 1), (k >> 1) & 1);
+          mbar_wait(bVfull, k & 1);
           const int stage = ring % kStages;
           mbar_wait(bQdOfull(stage), (ring / kStages) & 1);
           if (g > 0) mbar_wait(bSdPfree, (g - 1) & 1);
           tc_fence_after();
-          issue_SdP(stage);
+          issue_SdP(stage, sK);
+          if (w.n_it == 1) tc_commit_p(bVfree, lead);  // the item's last (only) dP: V may be replaced by the next item's
         }
+        first_issued = false;
+        bool have_next = false, next_valid = false;
         for (int it = 0; it < w.n_it; ++it, ++g) {
           const int rr = ring + it;
           const int stage = rr % kStages;
@@ -808,8 +835,31 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             mbar_wait(bSdPfree, g & 1);
             tc_fence_after();
             TRACE(5, it * 4 + 0);
-            issue_SdP(s1);
+            issue_SdP(s1, sK);
+            if (it + 2 == w.n_it) tc_commit_p(bVfree, lead);  // that was the item's last dP
             TRACE(5, it * 4 + 1);
+          } else {
+            // last tile of the item: the "next tile" is the first one of the CTA's next item.  Its K was prefetched
+            // into the other buffer, its V follows the dP MMA issued one tile ago; if both (and Q / dO) are there by
+            // now, S / dP of the next item are computed under this tile's math as well — otherwise after this item
+            have_next = true;
+            next_valid = next_item(k + 1, wn);
+            if (next_valid) {
+              const int turn = ring + w.n_it + 1;  // (+1: this item's rotation-table turn)
+              const int sn = turn % kStages;
+              bool ready = false;
+              for (int spin = 0; spin < 16 && !ready; ++spin)
+                ready = mbar_try_wait(bVfull, (k + 1) & 1) && mbar_try_wait(bKfull((k + 1) & 1), ((k + 1) >> 1) & 1) &&
+                        mbar_try_wait(bQdOfull(sn), (turn / kStages) & 1);
+              ready = __shfl_sync(0xffffffffu, ready ? 1 : 0, 0) != 0;  // (one decision for the warp)
+              if (ready) {
+                mbar_wait(bSdPfree, g & 1);
+                tc_fence_after();
+                issue_SdP(sn, sK0 + ((k + 1) & 1) * kTileBytes);
+                if (wn.n_it == 1) tc_commit_p(bVfree, lead);
+                first_issued = true;
+              }
+            }
           }
           mbar_wait(bPdSfull, g & 1);  // P / dS of this tile are in shared memory and tensor memory
           tc_fence_after();
@@ -843,21 +893,36 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           TRACE(5, it * 4 + 3);
         }
         tc_commit_p(bAccFull, lead);
+        tc_commit_p(bKfree(k & 1), lead);
         ring += w.n_it + 1;  // (+1: the rotation-table turn of the ring)
-        if (!next_item(k + 1, w)) break;
+        if (!have_next) next_valid = next_item(k + 1, wn);
+        if (!next_valid) break;
+        w = wn;
       }
     }
     __syncwarp();
   } else if (warp >= 8 && warp < 12) {
-    // ============================== dQ warpgroup (128 threads: one dQ row each) ==============================
-    // dQ of every tile: TMEM -> fp32 staging tile in shared memory -> one TMA reduce-add per 32-column half into
-    // dq_acc (fp32, L2-side add).  Runs beside the compute warpgroups, off their critical path.
-    reg_dealloc<96>();
+    // ============================== dQ warpgroup (128 threads: one row each) ==============================
+    // Everything that leaves tensor memory for global memory, off the compute warps' critical path:
+    //   per tile : dQ -> fp32 staging tile (two 32-column halves, one after the other) -> TMA reduce-add into dq_acc
+    //   per item : dV, dK (the transpose of the rotation applied) -> bf16 staging tile -> TMA store — while the compute
+    //              warps and the MMA issuer are already working on the CTA's next item
+    reg_dealloc<120>();  // (an explicit limit: ptxas would otherwise compile this branch under warpgroup 3's 56)
     const int r = tid & 127;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t stage_base = sbase + AttnBwdSmem::kdQ;
+    const uint32_t srow = sOut + r * 128;
+    // one staging tile: wait until the TMA that last read it is done, fill it (row r, eight 16-byte pieces), hand over
+    auto stage_rows = [&](const uint32_t* v32) {
+      if (r == 0) tma_store_wait_read<0>();
+      named_bar_sync(1, 128);
+#pragma unroll
+      for (int v = 0; v < 8; ++v)
+        st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(v32[v * 4], v32[v * 4 + 1], v32[v * 4 + 2], v32[v * 4 + 3]));
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+    };
     Item w = first;
-    int g = 0;
+    int g = 0, ring = 0;
     for (int k = 0;; ++k) {
       for (int it = 0; it < w.n_it; ++it, ++g) {
         mbar_wait(bdQfull, g & 1);
@@ -868,24 +933,74 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(bdQempty);
-        if (r == 0) tma_store_wait_read<0>();  // the previous reduce-add has finished reading the staging tile
-        named_bar_sync(1, 128);
-        const uint32_t srow = stage_base + r * 128;
-#pragma unroll
-        for (int v = 0; v < 8; ++v) {
-          st_shared_v4(srow + ((v ^ (r & 7)) << 4), make_uint4(q0r[v * 4], q0r[v * 4 + 1], q0r[v * 4 + 2], q0r[v * 4 + 3]));
-          st_shared_v4(srow + kTileBytes + ((v ^ (r & 7)) << 4),
-                       make_uint4(q1r[v * 4], q1r[v * 4 + 1], q1r[v * 4 + 2], q1r[v * 4 + 3]));
-        }
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
+        const int row0 = static_cast<int>(w.seq_row0) + (w.i_lo + it) * 128;
+        stage_rows(q0r);
         if (r == 0) {
-          const int row0 = static_cast<int>(w.seq_row0) + (w.i_lo + it) * 128;
-          tma_reduce_add_2d(&tm_dq, stage_base, w.h * 64, row0);
-          tma_reduce_add_2d(&tm_dq, stage_base + kTileBytes, w.h * 64 + 32, row0);
+          tma_reduce_add_2d(&tm_dq, sOut, w.h * 64, row0);
+          tma_store_commit();
+        }
+        stage_rows(q1r);
+        if (r == 0) {
+          tma_reduce_add_2d(&tm_dq, sOut, w.h * 64 + 32, row0);
           tma_store_commit();
         }
       }
+      // ---- the item's dV and dK
+      {
+        const int cs_turn = ring + w.n_it;
+        const int cs_stage = cs_turn % kStages;
+        const int row0 = static_cast<int>(w.seq_row0) + w.key0;
+        mbar_wait(bAccFull, k & 1);
+        tc_fence_after();
+        uint32_t a[32], o[32];  // (one 32-column row in flight at a time: this warpgroup has 128 registers per thread)
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          tmem_ld_32x32b_x32(tdV + lane_off + hf * 32, a);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 16; ++c) o[hf * 16 + c] = pack_bf16x2(__uint_as_float(a[2 * c]), __uint_as_float(a[2 * c + 1]));
+        }
+        stage_rows(o);
+        if (r == 0) {
+          tma_store_2d(&tm_dqkv, sOut, 2 * d + w.h * 64, row0);
+          tma_store_commit();
+        }
+        // (cos, sin) of key row r: the ring turn after the item's last Q / dO tile, 128B-swizzled rows of 32 floats
+        // (pairs 0..15 in the Q slot, pairs 16..31 in the dO slot); dK gets the transpose of the rotation in fp32
+        mbar_wait(bQdOfull(cs_stage), (cs_turn / kStages) & 1);
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          tmem_ld_32x32b_x32(tdK + lane_off + hf * 32, a);
+          tmem_ld_wait();
+          if (hf == 1) {
+            tc_fence_before();
+            mbar_arrive(bAccFree);  // the next item's dV / dK MMAs may overwrite the accumulators
+          }
+          const uint32_t cs_row = (hf == 0 ? sQ : sdO) + cs_stage * kTileBytes + r * 128;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const uint4 u0 = ld_shared_v4(cs_row + (((2 * v) ^ (r & 7)) << 4));
+            const uint4 u1 = ld_shared_v4(cs_row + (((2 * v + 1) ^ (r & 7)) << 4));
+            const float4 c0 = make_float4(__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w));
+            const float4 c1 = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w));
+            const float g0 = __uint_as_float(a[v * 8 + 0]), g1 = __uint_as_float(a[v * 8 + 1]);
+            const float g2 = __uint_as_float(a[v * 8 + 2]), g3 = __uint_as_float(a[v * 8 + 3]);
+            const float g4 = __uint_as_float(a[v * 8 + 4]), g5 = __uint_as_float(a[v * 8 + 5]);
+            const float g6 = __uint_as_float(a[v * 8 + 6]), g7 = __uint_as_float(a[v * 8 + 7]);
+            o[hf * 16 + v * 4 + 0] = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
+            o[hf * 16 + v * 4 + 1] = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
+            o[hf * 16 + v * 4 + 2] = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
+            o[hf * 16 + v * 4 + 3] = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
+          }
+        }
+        stage_rows(o);  // (its barriers also order every thread's rotation-table reads before the arrive below)
+        if (r == 0) {
+          mbar_arrive(bStageEmpty(cs_stage));  // the ring slot of the rotation table is free
+          tma_store_2d(&tm_dqkv, sOut, d + w.h * 64, row0);
+          tma_store_commit();
+        }
+      }
+      ring += w.n_it + 1;
       if (!next_item(k + 1, w)) break;
     }
     TRACE(7, 0);
@@ -893,13 +1008,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     TRACE(7, 1);
   } else if (warp < 8) {
     // ============================== compute warps (256 threads: row r, column half `half`) ==============================
-    reg_alloc<168>();
+    reg_alloc<160>();
     const int r = tid & 127;
     const int half = tid >> 7;
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     constexpr float c2 = kSoftmaxScale * kLog2e;
     Item w = first;
-    int g = 0, ring = 0;
+    int g = 0;
     for (int k = 0;; ++k) {
       const int b = w.b, h = w.h, i_lo = w.i_lo, n_it = w.n_it, key0 = w.key0;
       const long seq_row0 = w.seq_row0;
@@ -948,12 +1063,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           if (need_mask) chunk_p_ds<true>(sr, pr, c2, lse2, dlt_s, ds_t - key0 - col0, t - key0 - col0, pk_p[c], pk_ds[c]);
           else chunk_p_ds<false>(sr, pr, c2, lse2, dlt_s, 0, 0, pk_p[c], pk_ds[c]);
           // P leaves for shared memory chunk by chunk, under the math of the next chunk: its buffer is free as soon as
-          // the previous tile's dV MMAs are done (dS has to wait for dK and dQ as well) and, at the start of an item,
-          // once the previous item's dK / dV stores have read it
-          if (c == 0) {
-            if (g > 0) mbar_wait(bPfree, (g - 1) & 1);
-            if (it == 0 && k > 0) mbar_wait(bStaged, (k - 1) & 1);
-          }
+          // the previous tile's dV MMAs are done (dS has to wait for dK and dQ as well)
+          if (c == 0 && g > 0) mbar_wait(bPfree, (g - 1) & 1);
           {
             const uint32_t rowoff = half * kTileBytes + r * 128;
 #pragma unroll
@@ -989,64 +1100,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         mbar_arrive(bPdSfull);
         TRACE(2 + half, it * 4 + 3);
       }
-      // ---- the item's dK / dV (the next item's loads and first S / dP MMAs are already on their way)
-      TRACE(6, 0);
-      {
-        const int cs_stage = (ring + n_it) % kStages;
-        mbar_wait(bAccFull, k & 1);
-        tc_fence_after();
-        TRACE(6, 1);
-        // thread (r, half) owns key row r, 32 of the 64 head-dim columns of dK and dV
-        uint32_t kr[32], vr[32];
-        tmem_ld_32x32b_x32(tdK + lane_off + half * 32, kr);
-        tmem_ld_32x32b_x32(tdV + lane_off + half * 32, vr);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(bAccFree);  // the next item's dV / dK MMAs may overwrite the accumulators
-        TRACE(6, 6);
-        // (cos, sin) of this key row: in the ring slot after the last Q / dO tile, 128B-swizzled rows of 32 floats
-        mbar_wait(bQdOfull(cs_stage), ((ring + n_it) / kStages) & 1);
-        const uint32_t cs_row = (half == 0 ? sQ : sdO) + cs_stage * kTileBytes + r * 128;
-        // dV and dK (un-rotated) leave as two 128 x 64 bf16 tiles through the P buffer and one TMA store each
-        const uint32_t out_row = sP + r * 128;
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          uint4 o;
-          o.x = pack_bf16x2(__uint_as_float(vr[v * 8 + 0]), __uint_as_float(vr[v * 8 + 1]));
-          o.y = pack_bf16x2(__uint_as_float(vr[v * 8 + 2]), __uint_as_float(vr[v * 8 + 3]));
-          o.z = pack_bf16x2(__uint_as_float(vr[v * 8 + 4]), __uint_as_float(vr[v * 8 + 5]));
-          o.w = pack_bf16x2(__uint_as_float(vr[v * 8 + 6]), __uint_as_float(vr[v * 8 + 7]));
-          st_shared_v4(out_row + (((half * 4 + v) ^ (r & 7)) << 4), o);
-          // dK: transpose of the rotation, applied to the fp32 accumulators
-          const uint4 u0 = ld_shared_v4(cs_row + (((2 * v) ^ (r & 7)) << 4));
-          const uint4 u1 = ld_shared_v4(cs_row + (((2 * v + 1) ^ (r & 7)) << 4));
-          const float4 c0 = make_float4(__uint_as_float(u0.x), __uint_as_float(u0.y), __uint_as_float(u0.z), __uint_as_float(u0.w));
-          const float4 c1 = make_float4(__uint_as_float(u1.x), __uint_as_float(u1.y), __uint_as_float(u1.z), __uint_as_float(u1.w));
-          const float g0 = __uint_as_float(kr[v * 8 + 0]), g1 = __uint_as_float(kr[v * 8 + 1]);
-          const float g2 = __uint_as_float(kr[v * 8 + 2]), g3 = __uint_as_float(kr[v * 8 + 3]);
-          const float g4 = __uint_as_float(kr[v * 8 + 4]), g5 = __uint_as_float(kr[v * 8 + 5]);
-          const float g6 = __uint_as_float(kr[v * 8 + 6]), g7 = __uint_as_float(kr[v * 8 + 7]);
-          uint4 q;
-          q.x = pack_bf16x2(g0 * c0.x + g1 * c0.y, g1 * c0.x - g0 * c0.y);
-          q.y = pack_bf16x2(g2 * c0.z + g3 * c0.w, g3 * c0.z - g2 * c0.w);
-          q.z = pack_bf16x2(g4 * c1.x + g5 * c1.y, g5 * c1.x - g4 * c1.y);
-          q.w = pack_bf16x2(g6 * c1.z + g7 * c1.w, g7 * c1.z - g6 * c1.w);
-          st_shared_v4(out_row + kTileBytes + (((half * 4 + v) ^ (r & 7)) << 4), q);
-        }
-        fence_proxy_async_smem();
-        named_bar_sync(2, 256);
-        if (tid == 0) {
-          mbar_arrive(bStageEmpty(cs_stage));  // every thread has read its rotation-table row: the ring slot is free
-          const int row0 = static_cast<int>(seq_row0) + key0;
-          tma_store_2d(&tm_dqkv, sP, 2 * d + h * 64, row0);
-          tma_store_2d(&tm_dqkv, sP + kTileBytes, d + h * 64, row0);
-          tma_store_commit();
-          tma_store_wait_read<0>();  // the P buffer may be written again (and shared memory given up at the end)
-          mbar_arrive(bStaged);
-        }
-        TRACE(6, 2);
-      }
-      ring += n_it + 1;
+      // (the item's dK / dV leave through the dQ warpgroup: these warps go straight on to the next item)
 #ifdef PCV_TRACE
       ++trace_items;
 #endif
@@ -1204,12 +1258,11 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
     if (e != cudaSuccess) return static_cast<int>(e);
     attr = true;
   }
-  cudaError_t e = cudaMemsetAsync(dq_acc, 0, BT * d * sizeof(float), st);
-  if (e != cudaSuccess) return static_cast<int>(e);
   {
     const long threads = BT * n_heads * 8;
     attn_bwd_prep_kernel<<<static_cast<int>((threads + 255) / 256), 256, 0, st>>>(
-        static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, static_cast<int>(BT), T, n_heads);
+        static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, dq_acc,
+        static_cast<int>(BT), T, n_heads);
   }
   dim3 grid(n_heads, T / 128, B);
   attn_bwd_kernel<<<grid, kAttnBwdThreads, AttnBwdSmem::kBytes, st>>>(
