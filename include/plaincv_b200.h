@@ -49,6 +49,9 @@ int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
 int pcv_gemm_set_mode(int mode);
 /* Number of CTA-pair (tcgen05 cta_group::2) GEMM launches since load: lets a test assert which tiling ran. */
 long long pcv_gemm_pair_launch_count(void);
+/* Programmatic dependent launch for the GEMM / attention / RMSNorm kernels (their prologues may then run under the tail
+ * of the preceding kernel in the stream; results are identical).  0 = off (default), 1 = on. */
+int pcv_set_pdl(int on);
 
 /* fp32 master -> bf16 compute copy, zero-filling the padded tail columns: dst[rows][dst_ld] <- src[rows][src_ld][:cols].
  * Replaces flax's per-call promote_dtype of `kernel`/`embedding` (transformer.py: every nn.Dense / nn.Embed). */

@@ -285,8 +285,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_init(bPVdone(u), 1);
     }
     fence_mbar_init();
-    // Q and the first K / V tile are requested right away: their latency runs under the tensor-memory allocation and
-    // the block-wide barrier below
+  }
+  if (warp == 4) {
+    __syncwarp();
+    tmem_alloc<256>(tmem_ptr_smem);
+  }
+  // programmatic dependent launch: everything above may have run under the tail of the kernel that produces qkv
+  pdl_wait();
+  pdl_trigger();
+  if (warp == 4 && lane == 0) {
+    // Q and the first K / V tile are requested right away: their latency runs under the block-wide barrier below
     const int row0 = static_cast<int>(seq_row0);
     mbar_expect_tx(bQ, kTileBytes);
     tma_load_2d(sQ, &tm_qkv, bQ, h * 64, row0 + q0);
@@ -294,10 +302,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tma_load_2d(sK, &tm_qkv, bKfull(0), d + h * 64, row0 + jlo * 128);
     mbar_expect_tx(bVfull(0), kTileBytes);
     tma_load_2d(sV, &tm_qkv, bVfull(0), 2 * d + h * 64, row0 + jlo * 128);
-  }
-  if (warp == 4) {
-    __syncwarp();
-    tmem_alloc<256>(tmem_ptr_smem);
   }
   tc_fence_before();
   __syncthreads();
@@ -533,6 +537,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 // separate 64 MB memset node per layer cost 20 us at the 420M shape; here its stores ride under the loads).
 __global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
                                      float* __restrict__ delta, float* __restrict__ dq_acc, int BT, int T, int NH) {
+  pdl_wait();
+  pdl_trigger();
   const long gid = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
   const long item = gid >> 3;  // (row, head)
   const int c = static_cast<int>(gid & 7);
@@ -707,8 +713,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(bAccFree, 128);
     for (int u = 0; u < 4; ++u) mbar_init(bItem(u), 1);
     fence_mbar_init();
+  }
+  if (warp == 12) {
+    __syncwarp();
+    tmem_alloc<512>(tmem_ptr_smem);
+  }
+  // programmatic dependent launch: everything above may have run under the tail of the preceding kernel (the prep pass)
+  pdl_wait();
+  pdl_trigger();
+  if (warp == 12 && lane == 0) {
     // K, V and the first Q / dO tile of the first item are requested right away: their latency runs under the
-    // tensor-memory allocation and the block-wide barrier below
+    // block-wide barrier below
     const int row0 = static_cast<int>(first.seq_row0);
     mbar_expect_tx(bKfull(0), kTileBytes);
     tma_load_2d(sK0, &tm_qkv, bKfull(0), d + first.h * 64, row0 + first.key0);
@@ -717,10 +732,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_expect_tx(bQdOfull(0), 2 * kTileBytes);
     tma_load_2d(sQ, &tm_qkv, bQdOfull(0), first.h * 64, row0 + first.i_lo * 128);
     tma_load_2d(sdO, &tm_do, bQdOfull(0), first.h * 64, row0 + first.i_lo * 128);
-  }
-  if (warp == 12) {
-    __syncwarp();
-    tmem_alloc<512>(tmem_ptr_smem);
   }
   tc_fence_before();
   __syncthreads();
@@ -1126,6 +1137,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 // dqkv[:, q columns] = bf16( R(-theta) . dq_acc )    (dq_acc fp32 [B*T][d])
 __global__ void attn_bwd_dq_post_kernel(const float* __restrict__ dq_acc, const float* __restrict__ cos_sin,
                                         __nv_bfloat16* __restrict__ dqkv, long BT, int T, int d) {
+  pdl_wait();
+  pdl_trigger();
   const int vpr = d / 8;
   const long total = BT * vpr;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
@@ -1224,10 +1237,10 @@ extern "C" int pcv_attn_fwd(const void* qkv, const int32_t* doc_start, void* out
     attr = true;
   }
   dim3 grid(n_heads, B, T / 128);
-  attn_fwd_kernel<<<grid, kAttnThreads, AttnFwdSmem::kBytes, static_cast<cudaStream_t>(stream)>>>(
-      tm, tm_out, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
+  cudaError_t le = launch_pdl(attn_fwd_kernel, grid, dim3(kAttnThreads), AttnFwdSmem::kBytes, static_cast<cudaStream_t>(stream),
+                              tm, tm_out, doc_start, static_cast<__nv_bfloat16*>(out), lse, T, n_heads);
   count_launch();
-  return cuda_rc();
+  return le == cudaSuccess ? cuda_rc() : static_cast<int>(le);
 }
 
 extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out,
@@ -1260,20 +1273,26 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   }
   {
     const long threads = BT * n_heads * 8;
-    attn_bwd_prep_kernel<<<static_cast<int>((threads + 255) / 256), 256, 0, st>>>(
-        static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, dq_acc,
-        static_cast<int>(BT), T, n_heads);
+    cudaError_t le = launch_pdl(attn_bwd_prep_kernel, dim3(static_cast<unsigned>((threads + 255) / 256)), dim3(256), 0, st,
+                                static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, dq_acc,
+                                static_cast<int>(BT), T, n_heads);
+    if (le != cudaSuccess) return static_cast<int>(le);
   }
   dim3 grid(n_heads, T / 128, B);
-  attn_bwd_kernel<<<grid, kAttnBwdThreads, AttnBwdSmem::kBytes, st>>>(
-      tm_qkv, tm_do, tm_dq, tm_cs, tm_dqkv, cos_sin, doc_start, lse, delta, dq_acc,
-      static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
+  {
+    cudaError_t le = launch_pdl(attn_bwd_kernel, grid, dim3(kAttnBwdThreads), AttnBwdSmem::kBytes, st, tm_qkv, tm_do, tm_dq, tm_cs,
+                                tm_dqkv, cos_sin, doc_start, lse, static_cast<const float*>(delta), dq_acc,
+                                static_cast<__nv_bfloat16*>(dqkv), T, n_heads);
+    if (le != cudaSuccess) return static_cast<int>(le);
+  }
   {
     const long total = BT * (d / 8);
     long blocks = (total + 255) / 256;
     const long cap = static_cast<long>(num_sms()) * 16;
     if (blocks > cap) blocks = cap;
-    attn_bwd_dq_post_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(dq_acc, cos_sin, static_cast<__nv_bfloat16*>(dqkv), BT, T, d);
+    cudaError_t le = launch_pdl(attn_bwd_dq_post_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st,
+                                static_cast<const float*>(dq_acc), cos_sin, static_cast<__nv_bfloat16*>(dqkv), BT, T, d);
+    if (le != cudaSuccess) return static_cast<int>(le);
   }
   count_launch(3);
   return cuda_rc();

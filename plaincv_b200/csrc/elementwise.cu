@@ -88,6 +88,8 @@ __global__ void __launch_bounds__(256)
 rmsnorm_residual_fwd_kernel(const __nv_bfloat16* __restrict__ res_in, const __nv_bfloat16* __restrict__ delta,
                             const float* __restrict__ scale, __nv_bfloat16* __restrict__ res_out,
                             __nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out, int M, int d, float eps) {
+  pdl_wait();
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= M) return;
@@ -156,6 +158,8 @@ rmsnorm_residual_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfl
                             const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dres_in,
                             float* __restrict__ dscale, int M, int d) {
   extern __shared__ float sm_dscale[];  // [warps][d]
+  pdl_wait();
+  pdl_trigger();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int vpr = d / 8;
   float ds[VPL][8];
@@ -395,11 +399,11 @@ template <int VPL>
 static int launch_rms_fwd(const void* res_in, const void* delta, const float* scale, void* res_out, void* y, float* rstd,
                           int M, int d, float eps, cudaStream_t st) {
   const int rows_per_block = 8;
-  rmsnorm_residual_fwd_kernel<VPL><<<(M + rows_per_block - 1) / rows_per_block, 256, 0, st>>>(
-      static_cast<const __nv_bfloat16*>(res_in), static_cast<const __nv_bfloat16*>(delta), scale,
-      static_cast<__nv_bfloat16*>(res_out), static_cast<__nv_bfloat16*>(y), rstd, M, d, eps);
+  cudaError_t le = launch_pdl(rmsnorm_residual_fwd_kernel<VPL>, dim3((M + rows_per_block - 1) / rows_per_block), dim3(256), 0, st,
+                              static_cast<const __nv_bfloat16*>(res_in), static_cast<const __nv_bfloat16*>(delta), scale,
+                              static_cast<__nv_bfloat16*>(res_out), static_cast<__nv_bfloat16*>(y), rstd, M, d, eps);
   count_launch();
-  return cuda_rc();
+  return le == cudaSuccess ? cuda_rc() : static_cast<int>(le);
 }
 
 extern "C" int pcv_rmsnorm_residual_fwd(const void* res_in, const void* delta, const float* scale, void* res_out,
@@ -430,11 +434,11 @@ static int launch_rms_bwd(const void* dy, const void* dres_out, const void* res_
   const size_t smem = static_cast<size_t>(nwarps) * d * sizeof(float);
   auto kern = rmsnorm_residual_bwd_kernel<VPL>;
   if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-  kern<<<grid, threads, smem, st>>>(static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(dres_out),
-                                    static_cast<const __nv_bfloat16*>(res_out), scale, rstd,
-                                    static_cast<__nv_bfloat16*>(dres_in), dscale, M, d);
+  cudaError_t le = launch_pdl(kern, dim3(grid), dim3(threads), smem, st, static_cast<const __nv_bfloat16*>(dy),
+                              static_cast<const __nv_bfloat16*>(dres_out), static_cast<const __nv_bfloat16*>(res_out), scale, rstd,
+                              static_cast<__nv_bfloat16*>(dres_in), dscale, M, d);
   count_launch();
-  return cuda_rc();
+  return le == cudaSuccess ? cuda_rc() : static_cast<int>(le);
 }
 
 extern "C" int pcv_rmsnorm_residual_bwd(const void* dy, const void* dres_out, const void* res_out, const float* scale,

@@ -316,6 +316,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
+  pdl_wait();     // everything above ran under the previous kernel's tail; from here on its results are read
+  pdl_trigger();  // (after the wait: a dependent that starts early then knows every kernel before this one has completed)
 
   const int total_work = p.m_tiles * p.n_tiles * p.splits;
 
@@ -526,6 +528,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   cluster_sync_all();  // barriers of both CTAs initialised, both TMEM allocations done
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_generic;
+  pdl_wait();     // everything above ran under the previous kernel's tail; from here on its results are read
+  pdl_trigger();  // (after the wait: a dependent that starts early then knows every kernel before this one has completed)
 
   const int total_work = pair_total_work(p);
 
@@ -986,8 +990,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_set = true;
   }
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(ta, tb, p);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = launch_pdl(kern, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, st, ta, tb, p);
+  if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
 }
 
@@ -1032,8 +1036,9 @@ static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const 
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_set = true;
   }
-  kern<<<grid, kPairThreads, PairCfgT<EPI>::kSmemBytes, st>>>(ta, tb, o.bn, o.c, o.c2, o.x, p);  // __cluster_dims__(2,1,1): grid is even
-  cudaError_t e = cudaGetLastError();
+  // __cluster_dims__(2,1,1): grid is even
+  cudaError_t e = launch_pdl(kern, dim3(grid), dim3(kPairThreads), PairCfgT<EPI>::kSmemBytes, st, ta, tb, o.bn, o.c, o.c2, o.x, p);
+  if (e == cudaSuccess) e = cudaGetLastError();
   return e == cudaSuccess ? PCV_OK : static_cast<int>(e);
 }
 

@@ -95,6 +95,12 @@ __device__ __forceinline__ bool clc_query(uint32_t result_smem, int& x, int& y, 
   return ok != 0;
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// pdl_trigger: this CTA no longer holds back the launch of the next kernel in the stream (its CTAs start as SMs free up
+// and run to their own pdl_wait).  pdl_wait: everything the preceding kernels wrote is complete and visible.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // generic-proxy writes to smem -> visible to the async proxy (TMA / tcgen05 operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
