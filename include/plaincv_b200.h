@@ -26,6 +26,7 @@ extern "C" {
 #define PCV_ERR_ALIGN (-2)  /* pointer or leading dimension violates the 16-byte rule of TMA / vector access */
 #define PCV_ERR_TMAP (-3)   /* cuTensorMapEncodeTiled failed */
 #define PCV_ERR_DRIVER (-4) /* driver entry point unavailable */
+#define PCV_ERR_SCRATCH (-5) /* problem larger than the built-in scratch of a *_static entry point */
 
 /* GEMM epilogues */
 #define PCV_EPI_BF16 0       /* C bf16  = alpha * acc              */
@@ -112,6 +113,16 @@ int pcv_attn_fwd(const void* qkv, const int32_t* doc_start, void* out, float* ls
  * (zeroed here; dQ partials of the key tiles are reduce-added into it, then un-rotated). */
 int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out, const void* dout,
                  const float* lse, float* delta, float* dq_acc, void* dqkv, int B, int T, int n_heads, void* stream);
+
+/* pcv_attn_bwd without caller-supplied scratch and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  delta and the fp32 dQ accumulator live in a file-scope device array of the library:
+ * limit B*T*n_heads*64 <= 4,194,304 (e.g. 4096 tokens at d = 1024; 16.25 MiB held per GPU until the process exits),
+ * beyond it the call returns PCV_ERR_SCRATCH and launches nothing.  All calls share that array (it keeps the previous
+ * call's contents; what must start at zero is cleared by each call): calls that overlap on the GPU race — serialise
+ * them.  Same arguments, results and error codes as pcv_attn_bwd otherwise. */
+int pcv_attn_bwd_static(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out,
+                        const void* dout, const float* lse, void* dqkv, int B, int T, int n_heads, void* stream);
 
 /* Softmax cross-entropy over bf16 logits[M][ldl] (first V columns valid) with integer labels — _loss_and_acc,
  * train_lm.py:181-186 (fp32 logsumexp - logit[label], mean over all M tokens; acc = first-max argmax == label).

@@ -22,6 +22,7 @@ _ERR = {
     -2: "PCV_ERR_ALIGN (pointer or leading dimension violates the 16-byte rule)",
     -3: "PCV_ERR_TMAP (cuTensorMapEncodeTiled failed)",
     -4: "PCV_ERR_DRIVER (driver entry point unavailable)",
+    -5: "PCV_ERR_SCRATCH (problem larger than the built-in scratch of a *_static entry point)",
 }
 
 # name -> (restype, argtypes); mirrors include/plaincv_b200.h one to one
@@ -52,6 +53,8 @@ SIGNATURES = {
     "pcv_attn_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "pcv_attn_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                              c_int, c_int, c_int, c_void_p]),
+    "pcv_attn_bwd_static": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                    c_int, c_void_p]),
     "pcv_softmax_ce": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,
                                c_void_p]),
     "pcv_mean2": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -31,6 +31,7 @@
 #include "sm100.cuh"
 #include "pcv_internal.h"
 #include <math.h>
+#include <mutex>
 
 namespace pcv {
 
@@ -1296,4 +1297,59 @@ extern "C" int pcv_attn_bwd(const void* qkv, const float* cos_sin, const int32_t
   }
   count_launch(3);
   return cuda_rc();
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// pcv_attn_bwd_static: pcv_attn_bwd for callers that cannot allocate device memory (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  The two scratch tensors of the backward pass — the fp32 dQ
+// accumulator [B*T][d] and delta [B][N][T] — live in a file-scope device array instead of caller-supplied buffers.
+// No counterpart in the reference.
+//   * Limit: B*T*d <= 4,194,304 floats (e.g. 4096 tokens at d = 1024) — 16.25 MiB of device memory, held by every GPU
+//     that loads the library until the process exits.  Larger problems get PCV_ERR_SCRATCH.
+//   * Every call shares the array and finds the previous call's contents in it: the dQ accumulator is zero-filled by the
+//     prep kernel of each call before the main kernel reduce-adds into it, delta is overwritten in full.  Two calls that
+//     overlap on the GPU (different streams, no dependency) RACE on it: serialise them.
+//   * The entry point calls no cudaMalloc / cudaFree / allocating library routine.
+namespace pcv {
+constexpr size_t kBwdStaticDqFloats = size_t(4) << 20;       // dQ accumulator: B*T*d floats
+constexpr size_t kBwdStaticDeltaFloats = size_t(64) << 10;   // delta: B*N*T = B*T*d / 64 floats
+static __device__ __align__(256) float g_attn_bwd_scratch[kBwdStaticDqFloats + kBwdStaticDeltaFloats];
+
+// In host code `g_attn_bwd_scratch` is only a host-side stand-in for the symbol, not a device address: the address the
+// kernels need is asked for once per device, with that device current.
+static int attn_bwd_scratch_ptr(float** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float* ptrs[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= kMaxDevices) return PCV_ERR_ARG;
+  std::lock_guard<std::mutex> g(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_attn_bwd_scratch);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 255)) return PCV_ERR_ALIGN;
+    ptrs[dev] = static_cast<float*>(p);
+  }
+  *out = ptrs[dev];
+  return PCV_OK;
+}
+}  // namespace pcv
+
+extern "C" int pcv_attn_bwd_static(const void* qkv, const float* cos_sin, const int32_t* doc_start, const void* out,
+                                   const void* dout, const float* lse, void* dqkv, int B, int T, int n_heads,
+                                   void* stream) {
+  int rc = attn_check(B, T, n_heads);
+  if (rc) return rc;
+  const size_t dq_floats = static_cast<size_t>(B) * T * n_heads * 64;
+  const size_t delta_floats = static_cast<size_t>(B) * T * n_heads;
+  if (dq_floats > pcv::kBwdStaticDqFloats || delta_floats > pcv::kBwdStaticDeltaFloats) return PCV_ERR_SCRATCH;
+  float* base = nullptr;
+  rc = pcv::attn_bwd_scratch_ptr(&base);
+  if (rc) return rc;
+  // dq_acc at the start of the array (TMA reduce-add target: 256-byte aligned), delta behind its maximum extent
+  return pcv_attn_bwd(qkv, cos_sin, doc_start, out, dout, lse, base + pcv::kBwdStaticDqFloats, base, dqkv, B, T, n_heads,
+                      stream);
 }
