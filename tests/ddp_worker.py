@@ -12,6 +12,9 @@ import torch.distributed as dist  # noqa: E402
 
 
 def main():
+    import faulthandler
+    if int(os.environ.get("PCV_TEST_DUMP_AFTER", "0")) > 0:  # debugging aid: where is every thread after N seconds?
+        faulthandler.dump_traceback_later(int(os.environ["PCV_TEST_DUMP_AFTER"]), exit=True)
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -27,6 +30,7 @@ def main():
     model = Transformer(cfg, device=dev, seed=0)  # same seed on every rank: identical replicas
     batches = [synthetic_batch(B, T, V, seed=500 + k, doc_mean=300 if use_doc else None) for k in range(world)]
     for lpb in (1, 4, 8):
+        print(f"rank {rank}: layers_per_bucket {lpb}", file=sys.stderr, flush=True)
         res = ddp_gradient_check(model, T, use_doc, batches, rank, world, layers_per_bucket=lpb)
         res["layers_per_bucket"] = lpb
         if rank == 0:

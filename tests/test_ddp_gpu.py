@@ -32,7 +32,7 @@ def test_n_rank_gradients_equal_whole_batch_gradients(world, use_doc):
     env = dict(os.environ, PCV_TEST_DOC="1" if use_doc else "0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "tests", "ddp_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env, cwd=ROOT)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     lines = [json.loads(ln[len("DDPCHECK "):]) for ln in r.stdout.splitlines() if ln.startswith("DDPCHECK ")]
     assert [ln["layers_per_bucket"] for ln in lines] == [1, 4, 8]
@@ -40,9 +40,11 @@ def test_n_rank_gradients_equal_whole_batch_gradients(world, use_doc):
         print(res)
         assert res["world"] == world
         assert res["ranks_hold_identical_gradients"]
-        assert res["rel_l2_bf16_wire"] <= 4e-3, res
-        noise = res["rel_l2_rerun_noise"]
-        assert res["rel_l2_fp32_wire"] <= max(1e-5, 2 * noise), res
+        assert res["reducer_exact_rel_l2_bf16_wire"] <= 4e-3, res   # the reducer alone, on known numbers
+        assert res["reducer_exact_rel_l2_fp32_wire"] <= 1e-6, res
+        tol = max(4e-3, 1.5 * res["rel_l2_rerun_noise"])                # whole step: no tighter than its own noise
+        assert res["rel_l2_bf16_wire"] <= tol and res["rel_l2_fp32_wire"] <= tol, res
+        assert res["rel_l2_cuda_graph_vs_eager_bf16"] <= tol and res["cuda_graph_error"] is None, res
         assert res["overlap_off_equal"], res
         assert res["loss_abs_diff"] <= 1e-4, res
         assert res["ok"], res
