@@ -362,3 +362,9 @@ class Engine:
 
     def grads(self) -> Dict[str, torch.Tensor]:
         return self.model.export_flax_grads()
+
+    def close(self) -> None:
+        """Drop the captured CUDA graphs.  Call before torch.distributed.destroy_process_group(): a communicator whose
+        collectives live on inside a captured graph does not tear down (the call blocks)."""
+        self._graphs.clear()
+        self._graph_pool = None

@@ -35,8 +35,13 @@ def main():
         res["layers_per_bucket"] = lpb
         if rank == 0:
             print("DDPCHECK " + json.dumps(res), flush=True)
+    # No destroy_process_group(): tearing the NCCL communicator down while CUDA graphs that captured its collectives
+    # are still alive blocks forever (seen on 2 x B200, torch 2.11 / NCCL 2.28).  Everything is flushed; leave.
     dist.barrier()
-    dist.destroy_process_group()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
 
 
 if __name__ == "__main__":
