@@ -268,7 +268,7 @@ def attn_flops_per_token(c: dict, docs_lengths=None) -> float:
 
 
 _KERNEL_CLASSES = (("gemm_bf16", "gemm"), ("attn_fwd", "attn_fwd"), ("attn_bwd", "attn_bwd"), ("rmsnorm", "rmsnorm"),
-                   ("softmax_ce", "loss"), ("head_ce", "loss"), ("mean2", "loss"), ("nccl", "nccl"), ("cast", "cast"),
+                   ("softmax_ce", "loss"), ("ce_merge", "loss"), ("ce_apply", "loss"), ("ce_finish", "loss"), ("mean2", "loss"), ("nccl", "nccl"), ("cast", "cast"),
                    ("embed", "embed"), ("swiglu", "swiglu"), ("Memset", "memset"), ("Memcpy", "memcpy"))
 
 

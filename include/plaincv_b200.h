@@ -130,6 +130,21 @@ int pcv_attn_bwd_static(const void* qkv, const float* cos_sin, const int32_t* do
  * dlogits[M][ldl] = (softmax - onehot) * grad_scale (pad columns zero); dlogits may alias logits. */
 int pcv_softmax_ce(const void* logits, const int32_t* labels, void* dlogits, float* row_loss, float* row_correct,
                    int M, int V, int ldl, float grad_scale, void* stream);
+/* The LM head fused with softmax cross-entropy (models/LM/transformer.py:398-405 + train_lm.py:181-186), in two launches:
+ *  (1) pcv_gemm_bf16_ce: logits[M][ldl] = bf16(X[M,K] @ W) exactly as pcv_gemm_bf16 (W stored [K][ldw] when w_mn_major = 1 —
+ *      the lm_head kernel — or [N][ldw] when 0 — the tied embedding table), and, from the same epilogue registers, per
+ *      (row, 128-column slot) the online-softmax partials (max, sum exp(logit - max)) of the bf16-rounded logits over the
+ *      first n_valid columns: ce_ms = float2 [ceil(N/128)][M] (slot-major).  Always CTA-pair (cta_group::2) tiles.
+ *  (2) pcv_ce_from_stats: merges the slots into each row's log-sum-exp (ce_ms is consumed: its first M entries are
+ *      overwritten) and makes ONE streaming pass over the logits: reads the bf16
+ *      logits, writes dlogits = (softmax - onehot) * grad_scale (may alias logits; pad columns zero), row_loss = lse -
+ *      logit[label], row_correct = (first-max argmax == label).  One exponential per logit instead of the two of
+ *      pcv_softmax_ce, no per-row staging in shared memory.  Same results as pcv_gemm_bf16 + pcv_softmax_ce up to the
+ *      order of the fp32 sums. */
+int pcv_gemm_bf16_ce(const void* X, const void* W, void* logits, int M, int N, int K, int ldx, int ldw, int ldl,
+                     int w_mn_major, int n_valid, void* ce_ms, void* stream);
+int pcv_ce_from_stats(const void* logits, const int32_t* labels, void* ce_ms, int n_slots, void* dlogits,
+                      float* row_loss, float* row_correct, int M, int V, int ldl, float grad_scale, void* stream);
 /* out[0] = sum(row_loss)/M, out[1] = sum(row_correct)/M  (deterministic single-block reduction) */
 int pcv_mean2(const float* row_loss, const float* row_correct, float* out, int M, void* stream);
 

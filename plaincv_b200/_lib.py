@@ -34,6 +34,10 @@ SIGNATURES = {
     "pcv_gemm_set_mode": (c_int, [c_int]),
     "pcv_gemm_pair_launch_count": (c_longlong, []),
     "pcv_set_pdl": (c_int, [c_int]),
+    "pcv_gemm_bf16_ce": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                 c_void_p, c_void_p]),
+    "pcv_ce_from_stats": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                  c_float, c_void_p]),
     "pcv_cast_pad_bf16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "pcv_embed_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pcv_embed_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),

@@ -60,6 +60,10 @@ struct GemmParams {
   // CTA-pair kernel, tail of the persistent schedule: the tiles of the last, partial wave (index >= full_tiles) are cut
   // into two 256 x 128 halves when that lets every pair work on it (narrow = 1), instead of leaving pairs idle
   int full_tiles, narrow;
+  // EPI_BF16_CE only (LM head fused with the first half of softmax cross-entropy): per (row, 128-column slot) the
+  // maximum of the bf16-rounded logits and the sum of exp(logit - max), slot-major [slots][M]; columns >= ce_valid are pad
+  float2* ce_ms;
+  int ce_valid;
 #ifdef PCV_MEASURE
   // -DPCV_MEASURE builds only (never the shipped library): per-phase cycle counters of the epilogue warps
   // (pcv_gemm_set_profile) and switches that leave out operand loads / epilogue stores (pcv_gemm_set_mode(100 + flags))
@@ -77,6 +81,7 @@ struct GemmParams {
 constexpr int EPI_BF16_ROPE = 3;  // internal: PCV_EPI_BF16 + RoPE (pcv_gemm_bf16_rope)
 constexpr int EPI_SWIGLU = 4;     // internal: [g | u] = X W_gu written to C, h = silu(g) * u written to aux
 constexpr int EPI_DSWIGLU = 5;    // internal: dh = dM W_down^T kept in registers, [dg | du] written to C, gu read from aux
+constexpr int EPI_BF16_CE = 6;    // internal: PCV_EPI_BF16 + per-(row, 128-column slot) softmax partials (pcv_gemm_bf16_ce)
 
 // Work item -> (m tile, n tile, k split).  Tiles are visited in column-major order inside groups of kGroupM tile
 // rows, so the CTAs that run concurrently share a few A tiles AND a few B tiles (L2 reuse for wide outputs such as
@@ -271,6 +276,47 @@ __device__ __forceinline__ void dswiglu32(const uint32_t* r, float alpha, uint4*
       uw[k] = pack_bf16x2(du.x, du.y);
     }
   }
+}
+
+// Softmax partials of one row's 64 columns, from the bf16-ROUNDED logits q (8 x 16 bytes) — the values the loss is
+// defined on (the reference rounds the Dense output to bf16 before _loss_and_acc promotes it to fp32).  Columns
+// [0, n_valid) are real, the rest pad.  Merges (m, s) = (max, sum exp(x - max)) into the running pair.
+__device__ __forceinline__ void ce_slab_stats(const uint4* q, int n_valid, float& m_run, float& s_run) {
+  constexpr float kL2e = 1.4426950408889634f;
+  float x[64];
+#pragma unroll
+  for (int v = 0; v < 8; ++v) {
+    const uint32_t w4[4] = {q[v].x, q[v].y, q[v].z, q[v].w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 t = unpack_bf16x2(w4[k]);
+      x[v * 8 + 2 * k] = t.x;
+      x[v * 8 + 2 * k + 1] = t.y;
+    }
+  }
+  if (n_valid < 64) {
+#pragma unroll
+    for (int j = 0; j < 64; ++j)
+      if (j >= n_valid) x[j] = -3.0e38f;
+  }
+  float m = x[0];
+#pragma unroll
+  for (int j = 1; j < 64; ++j) m = fmaxf(m, x[j]);
+  const float m_new = fmaxf(m_run, m);
+  const float mb = m_new * kL2e;
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int j = 0; j < 64; j += 2) {
+    float e0, e1;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(fmaf(x[j], kL2e, -mb)));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(fmaf(x[j + 1], kL2e, -mb)));
+    s0 += e0;
+    s1 += e1;
+  }
+  float resc;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(resc) : "f"((m_run - m_new) * kL2e));  // 0 when m_run = -3e38 (first slab)
+  s_run = s_run * resc + s0 + s1;
+  m_run = m_new;
 }
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
@@ -803,8 +849,9 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           if (!PCV_DBG(p, 2)) put(&tma_x, qh, n0, row0);
         }
         if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
-      } else if constexpr (EPI == EPI_BF16_ROPE || EPI == PCV_EPI_BF16) {
+      } else if constexpr (EPI == EPI_BF16_ROPE || EPI == PCV_EPI_BF16 || EPI == EPI_BF16_CE) {
         const int n0 = n_blk * BN + wk.ncol0 + tcol;
+        float ce_m = -3.0e38f, ce_s = 0.f;  // EPI_BF16_CE: this row's partials over the warp's 128 columns
         // (cos, sin) of this row's position for the 32 pairs of a head: the same for every head of the tile, so they
         // are fetched once per tile, before the accumulator is waited for
         const bool rot = (EPI == EPI_BF16_ROPE) && n0 < p.rope_cols;
@@ -839,8 +886,17 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
             }
             if (prof) { const unsigned int t = clk32(); pf2 += t - pt; pt = t; }
             if (n0 + sl * 64 < p.N) put(&tma_c, q, n0 + sl * 64, row0);
+            if constexpr (EPI == EPI_BF16_CE) {
+              const int nv = p.ce_valid - (n0 + sl * 64);
+              if (nv > 0) ce_slab_stats(q, nv, ce_m, ce_s);
+            }
             if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
           }
+        }
+        if constexpr (EPI == EPI_BF16_CE) {
+          // slot = this warp's 128-column stripe of the row; slot-major so that a warp's 32 rows store 256 contiguous bytes
+          const int row = row0 + lane;
+          if (n0 < p.N && row < p.M) p.ce_ms[static_cast<size_t>(n0 >> 7) * p.M + row] = make_float2(ce_m, ce_s);
         }
       } else {  // fp32 store / fp32 reduce-add: boxes of 32 columns
         const int n0 = n_blk * BN + wk.ncol0 + tcol;
@@ -1058,6 +1114,9 @@ static int dispatch_epi_pair(int epi, const CUtensorMap& ta, const CUtensorMap& 
     case EPI_DSWIGLU:
       if constexpr (!A_MN && !B_MN) return launch_gemm_pair<A_MN, B_MN, EPI_DSWIGLU>(ta, tb, o, p, grid, st);
       else return PCV_ERR_ARG;
+    case EPI_BF16_CE:
+      if constexpr (!A_MN) return launch_gemm_pair<A_MN, B_MN, EPI_BF16_CE>(ta, tb, o, p, grid, st);
+      else return PCV_ERR_ARG;
   }
   return PCV_ERR_ARG;
 }
@@ -1121,13 +1180,13 @@ extern "C" int pcv_gemm_set_mode(int mode) {
 
 static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                      int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, const float* cos_sin, int T,
-                     int rope_cols, void* stream) {
+                     int rope_cols, void* stream, float2* ce_ms = nullptr, int ce_valid = 0) {
   using namespace pcv;
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return PCV_ERR_ARG;
   if (splits < 0) return PCV_ERR_ARG;
   if (splits == 0) splits = (epilogue == PCV_EPI_F32_ATOMIC) ? auto_splits(M, N, K) : 1;
   if (epilogue != PCV_EPI_F32_ATOMIC && splits != 1) return PCV_ERR_ARG;
-  const int vec = (epilogue == PCV_EPI_BF16 || epilogue == EPI_BF16_ROPE) ? 8 : 4;
+  const int vec = (epilogue == PCV_EPI_BF16 || epilogue == EPI_BF16_ROPE || epilogue == EPI_BF16_CE) ? 8 : 4;
   if (N % vec || ldc % vec || (reinterpret_cast<uintptr_t>(C) & 15)) return PCV_ERR_ALIGN;
 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -1139,7 +1198,8 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
     const int sp = (kb_total + kps - 1) / kps;
     const long t2 = static_cast<long>(m2) * n2 * sp;
     const int mode = g_gemm_mode.load(std::memory_order_relaxed);
-    const bool pair = mode == 2 || (mode == 0 && t2 >= num_sms() / 2);
+    // (the fused cross-entropy partials exist in the CTA-pair epilogue only)
+    const bool pair = mode == 2 || epilogue == EPI_BF16_CE || (mode == 0 && t2 >= num_sms() / 2);
     if (pair) {
       CUtensorMap ta, tb;
       int rc;
@@ -1158,7 +1218,9 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       p.cos_sin = cos_sin; p.T = T; p.rope_cols = rope_cols;
       p.aux = nullptr; p.ld_aux = 0; p.half_off = 0;
       PairOut o;
-      if (epilogue == PCV_EPI_BF16 || epilogue == EPI_BF16_ROPE) rc = get_tmap_2d_bf16(&o.c, C, M, N, ldc, 32);
+      p.ce_ms = ce_ms;
+      p.ce_valid = ce_valid;
+      if (epilogue == PCV_EPI_BF16 || epilogue == EPI_BF16_ROPE || epilogue == EPI_BF16_CE) rc = get_tmap_2d_bf16(&o.c, C, M, N, ldc, 32);
       else rc = get_tmap_2d_f32(&o.c, C, M, N, ldc, 32);
       if (rc) return rc;
       o.c2 = o.c;
@@ -1174,7 +1236,9 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
       {
         const long np = num_sms() / 2;
         const long rem = t2 % np;
-        if (g_gemm_tail.load(std::memory_order_relaxed) && sp == 1 && epilogue != PCV_EPI_F32_ATOMIC && t2 > np && rem > 0 && 2 * rem <= np) {
+        // (not with the fused cross-entropy partials: their slots are the 128-column stripes of full tiles)
+        if (g_gemm_tail.load(std::memory_order_relaxed) && sp == 1 && epilogue != PCV_EPI_F32_ATOMIC && epilogue != EPI_BF16_CE &&
+            t2 > np && rem > 0 && 2 * rem <= np) {
           p.full_tiles = static_cast<int>(t2 - rem);
           p.narrow = 1;
           if (!b_mn_major) {
@@ -1217,6 +1281,7 @@ static int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K,
   p.alpha = alpha;
   p.cos_sin = cos_sin; p.T = T; p.rope_cols = rope_cols;
   p.aux = nullptr; p.ld_aux = 0; p.half_off = 0;
+  p.ce_ms = nullptr; p.ce_valid = 0;
   const long total = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
   const int grid = static_cast<int>(total < num_sms() ? total : num_sms());
   count_launch();
@@ -1234,6 +1299,14 @@ extern "C" int pcv_gemm_bf16_rope(const void* X, const void* W, void* Y, int M, 
                                   const float* cos_sin, int T, int rope_cols, void* stream) {
   if (!cos_sin || T <= 0 || rope_cols < 0 || rope_cols > N || rope_cols % 64 || M % T) return PCV_ERR_ARG;
   return gemm_impl(X, W, Y, M, N, K, ldx, ldw, ldy, 0, 1, pcv::EPI_BF16_ROPE, 1, 1.0f, cos_sin, T, rope_cols, stream);
+}
+
+extern "C" int pcv_gemm_bf16_ce(const void* X, const void* W, void* logits, int M, int N, int K, int ldx, int ldw, int ldl,
+                                int w_mn_major, int n_valid, void* ce_ms, void* stream) {
+  if (!ce_ms || n_valid <= 0 || n_valid > N) return PCV_ERR_ARG;
+  if (reinterpret_cast<uintptr_t>(ce_ms) & 7) return PCV_ERR_ALIGN;
+  return gemm_impl(X, W, logits, M, N, K, ldx, ldw, ldl, 0, w_mn_major, pcv::EPI_BF16_CE, 1, 1.0f, nullptr, 1, 0, stream,
+                   static_cast<float2*>(ce_ms), n_valid);
 }
 
 // Fused SwiGLU GEMMs: always CTA-pair tiles (the gate | up pairing of the forward needs the two B halves of a pair).
@@ -1259,6 +1332,7 @@ static int gemm_swiglu_impl(bool bwd, const void* A, const void* W, void* C, voi
   p.alpha = alpha;
   p.cos_sin = nullptr; p.T = 1; p.rope_cols = 0;
   p.aux = aux; p.ld_aux = ld_aux; p.half_off = hid;
+  p.ce_ms = nullptr; p.ce_valid = 0;
   // outputs: the gate (dg) and the up (du) half of C = [M][2*hid] as two maps clipped at hid columns, and h
   PairOut o;
   __nv_bfloat16* cb = static_cast<__nv_bfloat16*>(C);

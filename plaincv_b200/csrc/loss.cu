@@ -160,6 +160,112 @@ softmax_ce_kernel(const __nv_bfloat16* __restrict__ logits, const int32_t* __res
   }
 }
 
+// Second half of the cross-entropy that starts in the LM-head GEMM epilogue (pcv_gemm_bf16_ce): per (row, 128-column
+// slot) the epilogue left (max, sum exp(logit - max)) of the bf16-rounded logits, slot-major [slots][M].  Three small
+// steps, none with a per-row serial prologue (a one-block-per-row form — merge, barrier, stream — ran at 2.0 TB/s: two
+// 62-register CTAs per SM could not hide the merge's dependent loads and its barrier in front of every row):
+//   ce_merge_kernel : one THREAD per row walks the slots (coalesced: slot-major) -> (lse, row max) into slot 0 of the
+//                     row, argmax candidate = INT_MAX
+//   ce_apply_kernel : grid-stride over all 16-byte vectors of logits[M][ldl]: d(logits) = (exp(logit - lse) - onehot) *
+//                     scale written in place, ONE exponential per logit; elements equal to the row max race for the
+//                     first-max argmax with atomicMin; the thread that holds the label column writes the row's loss
+//   ce_finish_kernel: row_correct = (argmax == label)
+__global__ void __launch_bounds__(256)
+ce_merge_kernel(float2* __restrict__ ce_ms, int n_slots, int M, int* __restrict__ arg) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= M) return;
+  float m = -3.0e38f, sum = 0.f;
+  for (int sl = 0; sl < n_slots; ++sl) {
+    const float2 ms = ce_ms[static_cast<size_t>(sl) * M + row];
+    const float nm = fmaxf(m, ms.x);
+    sum = sum * ex2_approx((m - nm) * kLog2eF) + ms.y * ex2_approx((ms.x - nm) * kLog2eF);
+    m = nm;
+  }
+  ce_ms[row] = make_float2(m + logf(sum), m);  // slot 0 of this row has been consumed: (lse, row max) take its place
+  arg[row] = 0x7fffffff;
+}
+
+__global__ void __launch_bounds__(256)
+ce_apply_kernel(const __nv_bfloat16* logits, const int32_t* __restrict__ labels, const float2* __restrict__ lse_max,
+                __nv_bfloat16* dlogits, float* __restrict__ row_loss, int* __restrict__ arg, int M, int V, int ldl,
+                float grad_scale) {
+  // work item = (row, chunk of kUnroll * 256 vectors): the row's constants and all index arithmetic are per item, the
+  // per-vector work is load, 8 exponentials, store
+  constexpr int kUnroll = 4;
+  constexpr int kChunk = kUnroll * 256;
+  const int nvec = ldl / 8;
+  const int nchunk = (nvec + kChunk - 1) / kChunk;
+  const long items = static_cast<long>(M) * nchunk;
+  for (long it = blockIdx.x; it < items; it += gridDim.x) {
+    const int row = static_cast<int>(it / nchunk);
+    const int c = static_cast<int>(it - static_cast<long>(row) * nchunk);
+    const uint4* src = reinterpret_cast<const uint4*>(logits + static_cast<long>(row) * ldl);
+    uint4* dst = reinterpret_cast<uint4*>(dlogits + static_cast<long>(row) * ldl);
+    const int vbase = c * kChunk + threadIdx.x;
+    uint4 raws[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int v = vbase + u * 256;
+      raws[u] = (v < nvec) ? src[v] : make_uint4(0, 0, 0, 0);
+    }
+    const float2 lm = __ldg(lse_max + row);
+    const int label = __ldg(labels + row);
+    const float lse2 = lm.x * kLog2eF;
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int v = vbase + u * 256;
+      if (v >= nvec) continue;  // (not `break`: it would keep raws[] dynamically indexed, i.e. in local memory)
+      const uint32_t w[4] = {raws[u].x, raws[u].y, raws[u].z, raws[u].w};
+      float f[8], g[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 t = unpack_bf16x2(w[j]);
+        f[2 * j] = t.x;
+        f[2 * j + 1] = t.y;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = ex2_approx(fmaf(f[j], kLog2eF, -lse2));
+      if (v * 8 + 8 > V) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v * 8 + j >= V) { g[j] = 0.f; f[j] = -3.0e38f; }
+      }
+      const float vm = fmaxf(fmaxf(fmaxf(f[0], f[1]), fmaxf(f[2], f[3])), fmaxf(fmaxf(f[4], f[5]), fmaxf(f[6], f[7])));
+      if (vm >= lm.y) {  // holds a row maximum: candidate for the first-max argmax
+        int a = 0x7fffffff;
+#pragma unroll
+        for (int j = 7; j >= 0; --j)
+          if (f[j] >= lm.y) a = v * 8 + j;
+        atomicMin(arg + row, a);
+      }
+      // one-hot and label pick as selects over all eight lanes (an `if (j == label & 7)` body is turned into a
+      // dynamically indexed access by the compiler, which puts f[] and g[] into local memory)
+      const int lj = (v == (label >> 3)) ? (label & 7) : -1;
+      float picked = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const bool hit = (j == lj);
+        picked += hit ? f[j] : 0.f;
+        g[j] = (g[j] - (hit ? 1.f : 0.f)) * grad_scale;
+      }
+      if (lj >= 0) row_loss[row] = lm.x - picked;
+      uint4 o;
+      o.x = pack_bf16x2(g[0], g[1]); o.y = pack_bf16x2(g[2], g[3]);
+      o.z = pack_bf16x2(g[4], g[5]); o.w = pack_bf16x2(g[6], g[7]);
+      dst[v] = o;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+ce_finish_kernel(const int* __restrict__ arg, const int32_t* __restrict__ labels, float* __restrict__ row_correct, int M) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row < M) {
+    const int a = arg[row];  // (row_correct aliases arg: read before write, one thread per element)
+    row_correct[row] = (a == labels[row]) ? 1.f : 0.f;
+  }
+}
+
 __global__ void __launch_bounds__(1024) mean2_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                                       float* __restrict__ out, int M) {
   __shared__ double sa[32], sb[32];
@@ -207,6 +313,31 @@ extern "C" int pcv_softmax_ce(const void* logits, const int32_t* labels, void* d
                                                        ldl, grad_scale);
   }
   count_launch();
+  return cuda_rc();
+}
+
+extern "C" int pcv_ce_from_stats(const void* logits, const int32_t* labels, void* ce_ms, int n_slots, void* dlogits,
+                                 float* row_loss, float* row_correct, int M, int V, int ldl, float grad_scale, void* stream) {
+  if (!logits || !labels || !ce_ms || !dlogits || !row_loss || !row_correct || M <= 0 || V <= 0 || V > ldl || n_slots <= 0)
+    return PCV_ERR_ARG;
+  if (n_slots != (ldl + 127) / 128) return PCV_ERR_ARG;
+  if (ldl % 8 || (reinterpret_cast<uintptr_t>(logits) & 15) || (reinterpret_cast<uintptr_t>(dlogits) & 15) ||
+      (reinterpret_cast<uintptr_t>(ce_ms) & 7) || (reinterpret_cast<uintptr_t>(row_correct) & 3))
+    return PCV_ERR_ALIGN;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int* arg = reinterpret_cast<int*>(row_correct);  // the argmax candidates live in row_correct until the last step
+  float2* ms = static_cast<float2*>(ce_ms);
+  const int rb = (M + 255) / 256;
+  ce_merge_kernel<<<rb, 256, 0, st>>>(ms, n_slots, M, arg);
+  const long items = static_cast<long>(M) * ((ldl / 8 + 1023) / 1024);
+  long blocks = items;
+  const long cap = static_cast<long>(num_sms()) * 8;
+  if (blocks > cap) blocks = cap;
+  ce_apply_kernel<<<static_cast<int>(blocks), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(logits), labels, ms,
+                                                            static_cast<__nv_bfloat16*>(dlogits), row_loss, arg, M, V, ldl,
+                                                            grad_scale);
+  ce_finish_kernel<<<rb, 256, 0, st>>>(arg, labels, row_correct, M);
+  count_launch(3);
   return cuda_rc();
 }
 

@@ -325,3 +325,72 @@ def test_attention_against_flash_attn_library(ops, B, T, NH):
     assert rel_l2(out, ref.reshape(B * T, d)) < 1e-2
     for name, sl, gr in (("dq", slice(0, d), q.grad), ("dk", slice(d, 2 * d), k.grad), ("dv", slice(2 * d, 3 * d), v.grad)):
         assert rel_l2(dqkv[:, sl], gr.reshape(B * T, d)) < 1.5e-2, name
+
+
+@pytest.mark.parametrize("M,V,tied", [(256, 50257, False), (512, 50280, False), (128, 1000, False), (192, 1003, True),
+                                      (16384, 50280, False)])
+def test_head_fused_with_cross_entropy(ops, M, V, tied):
+    """LM head fused with softmax cross-entropy (transformer.py:398-405 + train_lm.py:181-186): pcv_gemm_bf16_ce leaves
+    the per-(row, 128-column slot) online-softmax partials in the head GEMM's epilogue, pcv_ce_from_stats finishes in one
+    pass.  Against (a) the un-fused pair pcv_gemm_bf16 + pcv_softmax_ce — identical logits, loss / accuracy / d(logits)
+    equal up to fp32 summation order — and (b) the oracle's loss_and_acc on the same bf16 logits."""
+    class _Head:
+        pass
+    g = torch.Generator(device="cuda").manual_seed(21)
+    d = 256
+    vp = (V + 63) // 64 * 64
+    hf = torch.randn(M, d, device="cuda", generator=g).to(torch.bfloat16)
+    head = _Head()
+    head.tied, head.vocab, head.v_pad = tied, V, vp
+    if tied:  # table [V_pad, d], pad rows zero
+        w = torch.zeros(vp, d, device="cuda", dtype=torch.bfloat16)
+        w[:V] = (torch.randn(V, d, device="cuda", generator=g) * 0.3).to(torch.bfloat16)
+    else:     # lm_head kernel [d, V_pad], pad columns zero
+        w = torch.zeros(d, vp, device="cuda", dtype=torch.bfloat16)
+        w[:, :V] = (torch.randn(d, V, device="cuda", generator=g) * 0.3).to(torch.bfloat16)
+    head.w_lm = w
+    labels = torch.randint(0, V, (M,), device="cuda", generator=g, dtype=torch.int32)
+    labels[0] = V - 1
+    scale = 1.0 / M
+    ref_logits = ops.head_logits(hf, head)
+    logits, ce_ms = ops.head_logits_ce(hf, head)
+    assert torch.equal(logits, ref_logits)  # the fused epilogue stores the same bf16 logits
+    lf = ref_logits[:, :V].float()
+    out2_ref, dl_ref = ops.softmax_ce(ref_logits.clone(), labels, V, scale, True)
+    out2, dl = ops.ce_from_stats(logits, labels, ce_ms, V, scale)
+    torch.cuda.synchronize()
+    assert abs(float(out2[0]) - float(out2_ref[0])) < 2e-6 * abs(float(out2_ref[0]))
+    assert float(out2[1]) == float(out2_ref[1])
+    assert rel_l2(dl, dl_ref) < 2e-3  # bf16 outputs of two fp32 computations that differ in summation order
+    if vp > V:
+        assert float(dl[:, V:].float().abs().max()) == 0.0
+    if M <= 512:  # and against the oracle (fp32 softmax cross-entropy of the same bf16 logits, first-max argmax)
+        lo = lf.cpu().requires_grad_(True)
+        loss_o, acc_o = O.loss_and_acc(lo[None], labels.cpu()[None])
+        loss_o.backward()
+        assert abs(float(out2[0]) - float(loss_o)) < 1e-5 * float(loss_o)
+        assert float(out2[1]) == pytest.approx(float(acc_o), abs=1e-7)
+        assert rel_l2(dl[:, :V], lo.grad) < 6e-3
+
+
+def test_model_with_fused_head_ce_matches_unfused(ops, monkeypatch):
+    """The opt-in model path (PCV_HEAD_CE_FUSED=1): same loss, gradients within the run-to-run noise of the default."""
+    from plaincv_b200.engine import Engine
+    from plaincv_b200.model import ModelConfig, Transformer
+    cfg = ModelConfig(vocab_size=50257, seq_len=256, dim=256, expand=8 / 3, n_layers=2, n_heads=4)
+    model = Transformer(cfg, device="cuda", seed=0)
+    batch = O.synthetic_batch(4, 256, 50257, seed=3)
+    eng = Engine(model, seq_len=256)
+    monkeypatch.setattr(ops, "_HEAD_CE_FUSED", False)
+    l0, a0 = eng.compute_grads(batch)
+    g0 = model.flat_grad.clone()
+    monkeypatch.setattr(ops, "_HEAD_CE_FUSED", True)
+    n0 = _lib_count()
+    l1, a1 = eng.compute_grads(batch)
+    assert abs(float(l1) - float(l0)) < 2e-6 * float(l0) and float(a1) == float(a0)
+    assert rel_l2(model.flat_grad, g0) < 2e-3
+
+
+def _lib_count():
+    from plaincv_b200 import _lib
+    return _lib.load().pcv_launch_count()

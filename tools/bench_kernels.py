@@ -86,6 +86,37 @@ if which in ("all", "ew"):
     res["softmax_ce(+grad)"] = (ms, 2 * M * Vp * 2 / ms / 1e6, "GB/s")
     del logits
 
+if which == "ce":
+    # LM head + loss, un-fused (pcv_gemm_bf16 + pcv_softmax_ce) against fused (pcv_gemm_bf16_ce + pcv_ce_from_stats)
+    class _H:
+        pass
+    V = 50280
+    head = _H()
+    head.tied, head.vocab, head.v_pad = False, V, Vp
+    head.w_lm = (torch.randn(d, Vp, device=dev) * 0.02).to(bf)
+    hf = torch.randn(M, d, device=dev).to(bf)
+    labels = torch.randint(0, V, (M,), device=dev, dtype=torch.int32)
+    ms = timeit(lambda: ops.head_logits(hf, head))
+    res["head_gemm"] = (ms, 2.0 * M * d * Vp / ms / 1e9, "TFLOP/s")
+    ms = timeit(lambda: ops.head_logits_ce(hf, head))
+    res["head_gemm+ce_partials"] = (ms, 2.0 * M * d * Vp / ms / 1e9, "TFLOP/s")
+    logits, ce_ms = ops.head_logits_ce(hf, head)
+    ms = timeit(lambda: ops.softmax_ce(logits, labels, V, 1.0 / M, True))
+    res["softmax_ce(+grad)"] = (ms, 2 * M * Vp * 2 / ms / 1e6, "GB/s")
+    logits, ce_ms = ops.head_logits_ce(hf, head)
+    ms = timeit(lambda: ops.ce_from_stats(logits, labels, ce_ms, V, 1.0 / M))
+    res["ce_from_stats(+grad)"] = (ms, 2 * M * Vp * 2 / ms / 1e6, "GB/s")
+    # the same second half writing d(logits) to a separate buffer (is the in-place update what is slow?)
+    from plaincv_b200 import _lib as _L
+    lib = _L.load()
+    out_buf = torch.empty_like(logits)
+    rl = torch.empty(M, device=dev)
+    rc_ = torch.empty(M, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    ms = timeit(lambda: lib.pcv_ce_from_stats(logits.data_ptr(), labels.data_ptr(), ce_ms.data_ptr(), ce_ms.shape[0],
+                                              out_buf.data_ptr(), rl.data_ptr(), rc_.data_ptr(), M, V, Vp, 1.0 / M, st))
+    res["ce_from_stats out-of-place"] = (ms, 2 * M * Vp * 2 / ms / 1e6, "GB/s")
+
 if which == "fused":
     xg = torch.randn(M, d, device=dev).to(bf)
     wgu = (torch.randn(d, 2 * hp, device=dev) * 0.02).to(bf)
