@@ -240,7 +240,7 @@ def gemm_replay_ms(model, M: int, iters: int = 3) -> float:
             ops.linear_wgrad(x_d, x_d, g("layers_0.w_out"))
             dgrad(y_3d, layer.w_qkv, o_d)
             ops.linear_wgrad(x_d, y_3d, g("layers_0.w_qkv"))
-        lin(x_d, model.head.w_lm, y_V)
+        ops.head_logits_ce(x_d, model.head)               # LM head with the softmax partials in its epilogue
         dgrad(y_V, model.head.w_lm, o_d)
         ops.linear_wgrad(x_d, y_V, g("w_lm"))
 
@@ -473,7 +473,8 @@ def gpu_main(args) -> None:
     # captured on its second call
     ms_acc4, _, _ = timed(step_accum4, max(2, args.steps // 4), 3)
 
-    in_step = profile_one_step(w.step_resident)
+    # (skipped under ncu: two CUPTI clients cannot share the device)
+    in_step = {"skipped": True} if args.no_in_step_profile else profile_one_step(w.step_resident)
 
     ddp = None
     if world > 1 and not args.no_ddp_check:
@@ -580,6 +581,7 @@ def main() -> None:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra-configs", action="store_true", help="skip the C2 / C4 / C5 lines appended under 'configs'")
+    ap.add_argument("--no-in-step-profile", action="store_true", help="skip the CUPTI per-kernel profile of one step")
     ap.add_argument("--no-ddp-check", action="store_true", help="skip the N-rank gradient check run after the timed region")
     args = ap.parse_args()
     if args.impl == "reference":

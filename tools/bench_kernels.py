@@ -152,6 +152,11 @@ if which == "gemmstep":
     cs_t = ops.rope_table(64, T, 500000.0, dev)
     gq, go, ggu, gdn, glm = (torch.zeros_like(w, dtype=torch.float32) for w in (wq, wo, wgu, wdn, wlm))
 
+    class _H:
+        pass
+    head_lm = _H()
+    head_lm.tied, head_lm.vocab, head_lm.v_pad, head_lm.w_lm = False, 50280, Vp, wlm
+
     def layer_and_head():
         ops.linear_fwd_rope(xd, wq, cs_t, T, 2 * d)
         ops.linear_fwd(xd, wo)
@@ -165,7 +170,7 @@ if which == "gemmstep":
         ops.linear_wgrad(xd, xd, go)
         ops.linear_dgrad(y3, wq)
         ops.linear_wgrad(xd, y3, gq)
-        logits = ops.linear_fwd(xd, wlm)
+        logits, _ = ops.head_logits_ce(xd, head_lm)
         ops.linear_dgrad(logits, wlm)
         ops.linear_wgrad(xd, logits, glm)
 
