@@ -368,20 +368,25 @@ def make_timer(dev, local_rank: int, world: int, lib):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, eng=None):
+        """launches = this library's kernels executed inside the timed region: direct C-ABI launches
+        (pcv_launch_count) plus, when the engine replays its captured micro-step, the kernel nodes of every replay."""
+        def count():
+            return lib.pcv_launch_count() + (eng.replayed_launches if eng is not None else 0)
+
         for _ in range(warmup):
             fn()
         barrier()
         sampler = ClockSampler(local_rank)
         sampler.start()
-        l0 = lib.pcv_launch_count()
+        l0 = count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         barrier()
-        launches = lib.pcv_launch_count() - l0
+        launches = count() - l0
         clocks = sampler.stop()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
         if world > 1:
@@ -397,7 +402,7 @@ def extra_config_line(cname: str, dev, rank, world, timed, peaks, min_seconds: f
     w = Workload(cname, dev, rank, world)
     ms_probe, _, _ = timed(w.step_resident, 3, 3)
     steps = max(10, int(min_seconds * 1e3 / ms_probe) + 1)
-    ms, launches, clocks = timed(w.step_resident, steps, 1)
+    ms, launches, clocks = timed(w.step_resident, steps, 1, eng=w.eng)
     tok_s = w.tokens_per_step / (ms / 1e3)
     rec = {"workload": WORKLOAD_NAMES[cname], "value": tok_s, "unit": "tokens/s", "ms_per_step": ms, "steps": steps,
            "warmup": 7, "micro_batch_per_gpu": w.B, "seq_len": w.T, "n_gpus": world,
@@ -440,7 +445,7 @@ def gpu_main(args) -> None:
     comm_fp32 = w.comm_fp32
     tokens_per_step = w.tokens_per_step
 
-    ms_step, launches, clocks = timed(w.step_resident, args.steps, args.warmup)
+    ms_step, launches, clocks = timed(w.step_resident, args.steps, args.warmup, eng=w.eng)
 
     # end to end through the public API: host rows -> BatchFeeder (collate + _prepare_batch on a worker thread, pinned
     # ring, H2D on a copy stream) -> Engine.compute_grads -> loss read back, every step
@@ -514,7 +519,10 @@ def gpu_main(args) -> None:
             "e2e": {"value": tok_s_e2e, "unit": "tokens/s", "h2d_bytes_per_step": int(2 * B * T * 4 +
                                                                                        (B * T * 4 if c["doc"] else 0)),
                     "d2h_bytes_per_step": 8, "ms_per_step": ms_e2e},
-            "gpu_launches": int(launches), "clocks": clocks, "loss": loss_val,
+            "gpu_launches": int(launches),
+            "gpu_launches_note": "this library's kernels executed in the timed region: direct C-ABI launches + the "
+                                 "kernel nodes of every CUDA-graph replay of the micro-step",
+            "clocks": clocks, "loss": loss_val,
             "roofline": {"kernel": "pcv::gemm_bf16_pair_kernel (all Dense fwd/dgrad/wgrad launches of one step)",
                          "bound": "tensor", "achieved": gemm_tf, "peak": peaks["bf16_tflops_sustained"] / 1.0,
                          "unit": "TFLOP/s", "frac": gemm_tf / peaks["bf16_tflops_sustained"],

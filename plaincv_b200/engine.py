@@ -142,6 +142,7 @@ class _GraphedMicro:
         self.labels = torch.zeros(self.shape, dtype=torch.int32, device=dev)
         self.doc = torch.zeros(self.shape, dtype=torch.int32, device=dev) if self.has_doc else None
         self.stat = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.kernel_nodes = 0  # pcv_* launches recorded into the graph (one replay executes all of them)
 
     def _stage(self, inputs, labels, doc_start) -> None:
         self.inputs.copy_(inputs.view(self.shape), non_blocking=True)
@@ -158,12 +159,17 @@ class _GraphedMicro:
                 eng._graph_pool = torch.cuda.graph_pool_handle()
             # thread_local: other host threads (the BatchFeeder's worker stages the next batches meanwhile) may keep
             # calling CUDA; autograd's device thread launches onto the capturing stream and is captured with it
+            from . import _lib
+            lib = _lib.load()
+            n0 = lib.pcv_launch_count()
             with torch.cuda.graph(g, pool=eng._graph_pool, capture_error_mode="thread_local"):
                 self.stat.zero_()
                 eng._micro_body(self.inputs, self.labels, self.doc, self.accumulate, self.sync, self.loss_scale,
                                 self.stat)
+            self.kernel_nodes = int(lib.pcv_launch_count() - n0)
             self.graph = g
         self.graph.replay()
+        eng.replayed_launches += self.kernel_nodes
         stat += self.stat
 
 
@@ -224,6 +230,8 @@ class Engine:
         self.cuda_graph = bool(cuda_graph) and model.flat_grad.is_cuda
         self._graphs: Dict[tuple, "_GraphedMicro"] = {}
         self._graph_pool = None
+        # pcv_* kernel launches executed through graph replays (pcv_launch_count() only sees direct C-ABI calls)
+        self.replayed_launches = 0
 
     # ------------------------------------------------------------------ hooks
     def _arm_hooks(self, on: bool) -> None:
