@@ -46,7 +46,10 @@ int pcv_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
                   int a_mn_major, int b_mn_major, int epilogue, int splits, float alpha, void* stream);
 
 /* Tiling override for tests and benchmarks: 0 = automatic (CTA-pair 256x256 tiles, tcgen05 cta_group::2, whenever they
- * fill the machine; single-CTA 128xBN tiles otherwise), 1 = single-CTA tiles only, 2 = CTA-pair tiles always. */
+ * fill the machine; single-CTA 128xBN tiles otherwise), 1 = single-CTA tiles only, 2 = CTA-pair tiles always;
+ * 3 / 4 = keep / halve the tiles of a sparse last wave; 5 / 6 = static / dynamic tile schedule of the CTA-pair kernel
+ * (dynamic: one cluster launched per tile, running pairs take the tiles of the launches they cancel through cluster
+ * launch control; env PCV_GEMM_DYNAMIC).  Every setting computes the same product. */
 int pcv_gemm_set_mode(int mode);
 /* Number of CTA-pair (tcgen05 cta_group::2) GEMM launches since load: lets a test assert which tiling ran. */
 long long pcv_gemm_pair_launch_count(void);

@@ -12,6 +12,8 @@ from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libplaincv_b200.so")
+if os.environ.get("PCV_LIB_PATH"):  # debug / A-B builds of the same library (e.g. -DPCV_HANG_DEBUG); still no fallback
+    LIB_PATH = os.path.abspath(os.environ["PCV_LIB_PATH"])
 
 PCV_EPI_BF16 = 0
 PCV_EPI_F32_ATOMIC = 1

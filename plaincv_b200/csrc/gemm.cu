@@ -23,6 +23,7 @@
 #include "pcv_internal.h"
 
 #include <atomic>
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -60,6 +61,10 @@ struct GemmParams {
   // CTA-pair kernel, tail of the persistent schedule: the tiles of the last, partial wave (index >= full_tiles) are cut
   // into two 256 x 128 halves when that lets every pair work on it (narrow = 1), instead of leaving pairs idle
   int full_tiles, narrow;
+  // CTA-pair kernel: 1 = the launch order of the grid is the work queue (one cluster launched per work item; a running
+  // pair takes its own blockIdx first and then the launches it cancels through cluster launch control), 0 = every pair
+  // walks the fixed sequence pair, pair + npairs, ...
+  int dynamic;
   // EPI_BF16_CE only (LM head fused with the first half of softmax cross-entropy): per (row, 128-column slot) the
   // maximum of the bf16-rounded logits and the sum of exp(logit - max), slot-major [slots][M]; columns >= ce_valid are pad
   float2* ce_ms;
@@ -489,6 +494,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #ifndef PCV_DSWIGLU_STAGES
 #define PCV_DSWIGLU_STAGES 4
 #endif
+#ifndef PCV_GEMM_DYNAMIC_DEFAULT
+#define PCV_GEMM_DYNAMIC_DEFAULT 0
+#endif
 constexpr bool pair_epi_fused(int epi) { return epi == EPI_SWIGLU || epi == EPI_DSWIGLU; }
 template <int EPI>
 struct PairCfgT {
@@ -504,7 +512,8 @@ struct PairCfgT {
   static constexpr int kABytes = 128 * kBK * 2;  // this CTA's 128 rows of A
   static constexpr int kBBytes = 128 * kBK * 2;  // this CTA's 128 of the 256 B rows
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kBarBytes = 256;
+  static constexpr int kBarBytes = 1024;  // [0, 256) pipeline barriers, [256, 384) work-queue barriers, [512, 768) answers
+  static constexpr int kWorkSlots = 16;   // ring of cluster-launch-control answers (see next_work)
   static constexpr int kEpiWarps = 8;
   static constexpr int kEpiBoxBytes = 32 * 128;  // 32 rows x 128 B (one 128B-swizzled TMA box)
   static constexpr int kEpiBoxes = EPI == EPI_DSWIGLU ? 3 : (kFused ? PCV_SWIGLU_BOXES : 1);
@@ -538,12 +547,32 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * Cfg::kStages + 4);
   volatile uint32_t* tmem_ptr_generic =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_smem - smem_u32(smem_raw)));
+  auto work_bar = [&](int k) { return bar_base + 256u + 8u * (k & (Cfg::kWorkSlots - 1)); };    // (1; tx: 16 bytes)
+  auto work_slot = [&](int k) { return bar_base + 512u + 16u * (k & (Cfg::kWorkSlots - 1)); };  // 16-byte answers
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int pair = blockIdx.x >> 1;
   const int npairs = gridDim.x >> 1;
+  // The k-th work item of this pair (k = 0: its own blockIdx).  Static schedule: pair + k * npairs.  Dynamic schedule
+  // (p.dynamic): the answer to the cluster-launch-control request the producer issued while it loaded item k - 1 — the
+  // index of a cluster whose launch this pair cancelled, or "nothing left".  Every role of both CTAs reads the answers
+  // itself; they sit in a ring of kWorkSlots (item k -> slot k mod 16; the barrier's phase counts turns of the ring).
+  // The producer is at most kStages items ahead of the MMA issuer (one k-block per item at worst), the MMA issuer at
+  // most two accumulators ahead of the slowest epilogue warp of either CTA, so no reader is ever 16 items behind the
+  // request that reuses its slot.
+  auto next_work = [&](int k_next, int w_cur, int& w) -> bool {
+    if (!p.dynamic) {
+      w = w_cur + npairs;
+      return w < pair_total_work(p);
+    }
+    mbar_wait(work_bar(k_next), static_cast<uint32_t>((k_next - 1) / Cfg::kWorkSlots) & 1u);
+    int x, y, z;
+    if (!clc_query(work_slot(k_next), x, y, z)) return false;
+    w = x >> 1;
+    return true;
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -565,6 +594,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     if constexpr (EPI == EPI_DSWIGLU) {  // one per epilogue warp: its gate / up slab has landed
       for (int s = 0; s < Cfg::kEpiWarps; ++s) mbar_init(bar_base + 8u * (2 * Cfg::kStages + 5 + s), 1);
     }
+    for (int s = 0; s < Cfg::kWorkSlots; ++s) mbar_init(work_bar(s), 1);  // this CTA's producer: arrive.expect_tx(16)
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -584,7 +614,15 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       // ===================== TMA producer (both CTAs; completion lands on the leader's barrier) =====================
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = pair; w < total_work; w += npairs) {
+      int w = pair;
+      for (int k = 0; w < total_work; ++k) {
+        if (p.dynamic) {
+          // ask for the item after this one now (the answer to the request for THIS item was a success, so another
+          // request is allowed): it is there long before any role needs it.  Both CTAs arm their own barrier; the
+          // leader's request is answered in both CTAs' shared memory
+          mbar_expect_tx(work_bar(k + 1), 16);
+          if (rank == 0) clc_try_cancel_cluster(work_slot(k + 1), work_bar(k + 1));
+        }
         const PairWork wk = decode_pair_work(p, w);
         const int kb0 = wk.split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
@@ -624,6 +662,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
         }
+        if (!next_work(k + 1, w, w)) break;
       }
     }
     __syncwarp();
@@ -637,8 +676,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       constexpr uint32_t a_lbo = A_MN ? 64 * kBK * 2 : 16, b_lbo = B_MN ? 64 * kBK * 2 : 16;
       int stage = 0;
       uint32_t phase = 0;
-      int it = 0;
-      for (int w = pair; w < total_work; w += npairs, ++it) {
+      int w = pair;
+      for (int it = 0; w < total_work; ++it) {
         const PairWork wk = decode_pair_work(p, w);
         const int kb0 = wk.split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
@@ -663,6 +702,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1u; }
         }
         tc_commit_pair(tmem_full_bar(acc), 3);  // accumulator complete -> both CTAs' epilogues
+        if (!next_work(it + 1, w, w)) break;
       }
     }
     __syncwarp();
@@ -713,13 +753,17 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         c = wk.n_blk * BN + hh * 128 + sl * 64;
         return c < p.N && r < p.M;
       };
-      auto seek = [&](int& w, int& sl, int& c, int& r) -> bool {  // first slab at or after (w, sl) that exists
-        while (w < total_work) {
+      // first slab at or after slab sl of this pair's k-th work item (= w) that exists; false: no work is left
+      auto seek = [&](int& k, int& w, int& sl, int& c, int& r) -> bool {
+        while (true) {
           if (coords(w, sl, c, r)) return true;
           if (sl == 0) sl = 1;
-          else { sl = 0; w += npairs; }
+          else {
+            sl = 0;
+            if (!next_work(k + 1, w, w)) return false;
+            ++k;
+          }
         }
-        return false;
       };
       auto request = [&](int c, int r) {  // lane 0
         if (PCV_DBG(p, 8)) return;
@@ -727,10 +771,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
         tma_load_2d(box_g, &tma_x, ld_bar, c, r);
         tma_load_2d(box_u, &tma_bn, ld_bar, c, r);
       };
-      int nw = pair, nsl = 0, nc = 0, nr = 0;  // the slab whose gate / up values are on their way
-      if (seek(nw, nsl, nc, nr) && lane == 0) request(nc, nr);
-      int it = 0;
-      for (int w = pair; w < total_work; w += npairs, ++it) {
+      int nk = 0, nw = pair, nsl = 0, nc = 0, nr = 0;  // the slab whose gate / up values are on their way
+      if (seek(nk, nw, nsl, nc, nr) && lane == 0) request(nc, nr);
+      int w = pair;
+      for (int it = 0; w < total_work; ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BN + hh * 128;
@@ -764,11 +808,17 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           }
           __syncwarp();
           // both input boxes are in registers: the slab after this one can be on its way during the math
+          nk = it;
           nw = w;
           nsl = sl;
+          bool more = true;
           if (nsl == 0) nsl = 1;
-          else { nsl = 0; nw += npairs; }
-          if (seek(nw, nsl, nc, nr) && lane == 0) request(nc, nr);
+          else {
+            nsl = 0;
+            more = next_work(nk + 1, nw, nw);
+            ++nk;
+          }
+          if (more && seek(nk, nw, nsl, nc, nr) && lane == 0) request(nc, nr);
           if (prof) { const unsigned int t = clk32(); pf1 += t - pt; pt = t; }  // lds + issue of the next slab's loads
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
@@ -800,10 +850,11 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           }
           if (prof) { const unsigned int t = clk32(); pf3 += t - pt; pt = t; }
         }
+        if (!next_work(it + 1, w, w)) break;
       }
     } else {
-    int it = 0;
-    for (int w = pair; w < total_work; w += npairs, ++it) {
+    int w = pair;
+    for (int it = 0; w < total_work; ++it) {
       const PairWork wk = decode_pair_work(p, w);
       const int m_blk = wk.m_blk, n_blk = wk.n_blk;
       const int acc = it & 1;
@@ -915,6 +966,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
           }
         }
       }
+      if (!next_work(it + 1, w, w)) break;
     }
     }  // EPI != EPI_DSWIGLU
 #ifdef PCV_MEASURE
@@ -1121,8 +1173,31 @@ static int dispatch_epi_pair(int epi, const CUtensorMap& ta, const CUtensorMap& 
   return PCV_ERR_ARG;
 }
 
+// Tile schedule of the CTA-pair kernel (pcv_gemm_set_mode(5 / 6) or env PCV_GEMM_DYNAMIC=0 / 1, read once): 0 = static
+// persistent (one pair per TPC, tiles dealt round-robin), 1 = dynamic (one cluster LAUNCHED per work item; running pairs
+// cancel the launches behind them and take their tiles — pairs that start late or lose their SMs to another kernel,
+// e.g. an NCCL all-reduce or the side-stream wgrad GEMM, simply take fewer tiles instead of holding up a whole wave).
+static std::atomic<int> g_gemm_dynamic{-1};
+static int gemm_dynamic() {
+  int v = g_gemm_dynamic.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("PCV_GEMM_DYNAMIC");
+    v = e ? (atoi(e) != 0 ? 1 : 0) : PCV_GEMM_DYNAMIC_DEFAULT;
+    g_gemm_dynamic.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
 static int dispatch_major_pair(int a_mn, int b_mn, int epi, const CUtensorMap& ta, const CUtensorMap& tb,
-                               const PairOut& o, const GemmParams& p, int grid, cudaStream_t st) {
+                               const PairOut& o, const GemmParams& p_in, int grid, cudaStream_t st) {
+  GemmParams p = p_in;
+  p.dynamic = gemm_dynamic();
+  if (p.dynamic) {
+    const long tiles = static_cast<long>(p.m_tiles) * p.n_tiles * p.splits;
+    const long work = p.narrow ? p.full_tiles + 2 * (tiles - p.full_tiles) : tiles;
+    if (work > 0x3fffffffL) return PCV_ERR_ARG;
+    grid = static_cast<int>(2 * work);
+  }
   if (!a_mn && !b_mn) return dispatch_epi_pair<false, false>(epi, ta, tb, o, p, grid, st);
   if (!a_mn && b_mn) return dispatch_epi_pair<false, true>(epi, ta, tb, o, p, grid, st);
   if (a_mn && !b_mn) return dispatch_epi_pair<true, false>(epi, ta, tb, o, p, grid, st);
@@ -1172,8 +1247,9 @@ extern "C" int pcv_gemm_set_mode(int mode) {
 #ifdef PCV_MEASURE
   if (mode >= 100 && mode < 356) { pcv::g_gemm_dbg = mode - 100; return PCV_OK; }
 #endif
-  if (mode < 0 || mode > 4) return PCV_ERR_ARG;
-  if (mode >= 3) pcv::g_gemm_tail.store(mode == 4, std::memory_order_relaxed);
+  if (mode < 0 || mode > 6) return PCV_ERR_ARG;
+  if (mode >= 5) pcv::g_gemm_dynamic.store(mode == 6, std::memory_order_relaxed);
+  else if (mode >= 3) pcv::g_gemm_tail.store(mode == 4, std::memory_order_relaxed);
   else pcv::g_gemm_mode.store(mode, std::memory_order_relaxed);
   return PCV_OK;
 }

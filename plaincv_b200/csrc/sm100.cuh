@@ -76,6 +76,14 @@ __device__ __forceinline__ void clc_try_cancel(uint32_t result_smem, uint32_t ba
   asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
                ::"r"(result_smem), "r"(bar) : "memory");
 }
+// The same request on behalf of a whole cluster: the answer is written to `result_smem` (same offset) in EVERY CTA of the
+// requesting cluster and completes 16 transaction bytes on `bar` (same offset) in each of them; the id returned by
+// clc_query is that of the cancelled cluster's first CTA.  No CTA of the cluster may have exited.
+__device__ __forceinline__ void clc_try_cancel_cluster(uint32_t result_smem, uint32_t bar) {
+  asm volatile(
+      "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 [%0], [%1];"
+      ::"r"(result_smem), "r"(bar) : "memory");
+}
 // -> true and the cancelled CTA's blockIdx if the attempt answered in `result_smem` succeeded
 __device__ __forceinline__ bool clc_query(uint32_t result_smem, int& x, int& y, int& z) {
   uint32_t ok, bx = 0, by = 0, bz = 0;

@@ -65,10 +65,10 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
     1. the overlapped reducer with bf16 on the wire (the default), with fp32 on the wire, and with the overlap off
        (buckets reduced after backward) each produce rank-averaged gradients from this rank's shard;
     2. this rank alone accumulates all `world` micro-batches (sync=False, loss_scale 1/world): the gradient of the
-       whole global batch — twice, to measure the run-to-run noise of the fp32 reduce-adds (split-K wgrad, dQ);
+       whole global batch — three times, to measure the run-to-run noise of the fp32 reduce-adds (split-K wgrad, dQ);
     3. relative L2 distances over the whole flat gradient buffer, worst rank reported (MAX all-reduce).
-    Tolerances (asserted by the callers): bf16 wire <= 4e-3, fp32 wire <= max(1e-5, 2 x noise), overlap off vs on
-    <= max(1e-5, 2 x noise) for the same wire format."""
+    Tolerances: see `tolerance` in the result (the reducer alone is checked exactly by reducer_exact_check; the
+    whole-step distances are held to max(4e-3, 2 x the measured run-to-run noise))."""
     assert len(global_batches) == world
     mine = global_batches[rank]
     out: Dict[str, object] = {}
@@ -111,10 +111,14 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
 
     g_ref, loss_ref = whole_batch()
     g_ref2, _ = whole_batch()
+    g_ref3, _ = whole_batch()
+    # run-to-run noise of the SAME single-rank step: the largest of the three pairwise distances (one pair is a noisy
+    # estimate: on 2 GPUs single samples between 2.6e-3 and 5.7e-3 were seen for the same 9-layer step)
+    noise_local = max(_rel_l2(g_ref2, g_ref), _rel_l2(g_ref3, g_ref), _rel_l2(g_ref3, g_ref2))
 
     vals = torch.tensor([
         _rel_l2(g_bf16, g_ref), _rel_l2(g_fp32, g_ref), _rel_l2(g_bf16_off, g_bf16), _rel_l2(g_fp32_off, g_fp32),
-        _rel_l2(g_ref2, g_ref), abs(loss_ddp - loss_ref), abs(loss_ddp32 - loss_ref),
+        noise_local, abs(loss_ddp - loss_ref), abs(loss_ddp32 - loss_ref),
         _rel_l2(g_graph, g_bf16) if g_graph is not None else float("inf"), abs(loss_graph - loss_ddp),
     ], dtype=torch.float64, device=model.flat_grad.device)
     # ranks must also agree with each other bit for bit after the all-reduce: compare a checksum of the averaged buffer
@@ -134,7 +138,7 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
         dist.all_reduce(ex, op=dist.ReduceOp.MAX, group=process_group)
     ex_bf16, ex_fp32, ex_uncovered = (float(x) for x in ex)
     # whole-step comparisons cannot be tighter than two runs of the SAME single-rank step are to each other
-    step_tol = max(4e-3, 1.5 * noise)
+    step_tol = max(4e-3, 2.0 * noise)
     out.update({
         "world": world, "micro_batches_per_rank": 1,
         "rel_l2_bf16_wire": v[0], "rel_l2_fp32_wire": v[1],
@@ -150,8 +154,8 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
                    and float(cmin) == float(cmax)),
         "tolerance": "reducer alone on known numbers (no noise): bf16 wire <= 4e-3, fp32 wire <= 1e-6 of the exact mean; "
                      "whole step (bf16 / fp32 wire, overlap off, CUDA-graph replay, each against the single-rank gradient "
-                     "of the whole global batch or its eager twin) <= max(4e-3, 1.5 x rel_l2_rerun_noise): two runs of "
-                     "the same single-rank step differ by the order of fp32 reduce-adds (split-K wgrad, dQ), which "
+                     "of the whole global batch or its eager twin) <= max(4e-3, 2 x rel_l2_rerun_noise), the noise being the "
+                     "largest pairwise distance of three runs of the same single-rank step: such runs differ by the order of fp32 reduce-adds (split-K wgrad, dQ), which "
                      "bf16 roundings amplify layer by layer; loss |diff| <= 1e-4",
     })
     return out

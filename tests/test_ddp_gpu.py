@@ -42,7 +42,7 @@ def test_n_rank_gradients_equal_whole_batch_gradients(world, use_doc):
         assert res["ranks_hold_identical_gradients"]
         assert res["reducer_exact_rel_l2_bf16_wire"] <= 4e-3, res   # the reducer alone, on known numbers
         assert res["reducer_exact_rel_l2_fp32_wire"] <= 1e-6, res
-        tol = max(4e-3, 1.5 * res["rel_l2_rerun_noise"])                # whole step: no tighter than its own noise
+        tol = max(4e-3, 2.0 * res["rel_l2_rerun_noise"])                # whole step: no tighter than its own noise
         assert res["rel_l2_bf16_wire"] <= tol and res["rel_l2_fp32_wire"] <= tol, res
         assert res["rel_l2_cuda_graph_vs_eager_bf16"] <= tol and res["cuda_graph_error"] is None, res
         assert res["overlap_off_equal"], res

@@ -16,6 +16,8 @@ only run when a leaf exceeds 1e-2)."""
 import math
 
 import numpy as np
+import os
+
 import pytest
 import torch
 
@@ -179,12 +181,13 @@ _GEMM_CASES = [
 ]
 
 
-@pytest.mark.parametrize("mode", [1, 2], ids=["single_cta", "cta_pair"])
+@pytest.mark.parametrize("mode", [1, 2, 26], ids=["single_cta", "cta_pair", "cta_pair_dynamic"])
 @pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 0), (1, 1)])
 def test_gemm_cases_both_tilings(mode, a_mn, b_mn):
     """pcv_gemm_bf16 for every operand-major combination (forward = A K-major / B MN-major, dgrad = K / K, wgrad =
-    MN / MN) under both tilings, against fp32 matmul of the same bf16 inputs.  ld = extent rounded up to 8 + 8 (TMA's
-    16-byte rule, and rows that do not end where the matrix does)."""
+    MN / MN) under both tilings — the CTA-pair one with the static and with the dynamic (cluster-launch-control) tile
+    schedule — against fp32 matmul of the same bf16 inputs.  ld = extent rounded up to 8 + 8 (TMA's 16-byte rule, and
+    rows that do not end where the matrix does)."""
     from plaincv_b200 import ops
     torch.backends.cuda.matmul.allow_tf32 = False
     lib = _lib()
@@ -193,6 +196,10 @@ def test_gemm_cases_both_tilings(mode, a_mn, b_mn):
     def pad8(n):
         return (n + 7) // 8 * 8 + 8
 
+    dynamic = mode == 26
+    if dynamic:
+        mode = 2
+        lib.pcv_gemm_set_mode(6)
     lib.pcv_gemm_set_mode(mode)
     try:
         for (M, N, K, epi, splits) in _GEMM_CASES:
@@ -226,3 +233,4 @@ def test_gemm_cases_both_tilings(mode, a_mn, b_mn):
             assert torch.equal(C[:, Np:], C0[:, Np:]), (M, N, K, "wrote past the matrix")
     finally:
         lib.pcv_gemm_set_mode(0)
+        lib.pcv_gemm_set_mode(6 if os.environ.get("PCV_GEMM_DYNAMIC", "0") not in ("", "0") else 5)
