@@ -221,6 +221,13 @@ class _HeadHandles:
     __slots__ = ("out_norm", "w_lm", "g_out_norm", "g_lm", "vocab", "v_pad", "tied", "on_grads_ready")
 
 
+_T_TILE = 128  # query / key tile of the attention kernels
+
+
+def _round_up(n: int, m: int) -> int:
+    return (n + m - 1) // m * m
+
+
 class _Runtime:
     """Per-call constants shared by every block of one forward pass."""
 
@@ -261,7 +268,8 @@ class Transformer(nn.Module):
             node.register_parameter(parts[-1], p)
             self._flax_names[v.name] = ".".join(parts)
         self._params_by_flax = dict(zip(self._flax_names.keys(), [self.get_parameter(n) for n in self._flax_names.values()]))
-        self.cos_sin = ops.rope_table(cfg.head_dim, cfg.seq_len, cfg.rope_theta, device)
+        # (rows up to the next multiple of the attention tile: shorter or ragged sequences run padded, _prep_padded)
+        self.cos_sin = ops.rope_table(cfg.head_dim, _round_up(cfg.seq_len, _T_TILE), cfg.rope_theta, device)
         self._build_handles()
         self.reset_parameters(seed)
         self._attach_grads()
@@ -380,6 +388,22 @@ class Transformer(nn.Module):
                 raise ValueError("doc_start must have B*T entries")
         return ids, B, T, doc_start
 
+    def _prep_padded(self, input_ids, attn_mask, doc_lengths, doc_start):
+        """_prep_inputs for any T <= seq_len (the reference slices freqs_cis to the batch's length,
+        transformer.py:373-374): the attention kernels tile queries and keys by 128, so a ragged T runs as
+        T_run = T rounded up, every sequence right-padded with token 0.  Causality keeps real positions from ever seeing
+        a pad key, position t keeps rotation t (rows are b * T_run + t), so real rows are exactly what the un-padded
+        computation gives; the callers drop the pad rows (logits) or keep them out of the loss and zero their
+        d(logits) (ops._ce_means).  -> (ids, B, T, T_run, doc_start) with ids / doc_start of B * T_run entries."""
+        ids, B, T, doc_start = self._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
+        T_run = _round_up(T, _T_TILE)
+        if T_run != T:
+            ids = torch.nn.functional.pad(ids.view(B, T), (0, T_run - T)).contiguous().view(-1)
+            if doc_start is not None:  # every pad position is a document of its own
+                tail = torch.arange(T, T_run, device=ids.device, dtype=torch.int32).expand(B, T_run - T)
+                doc_start = torch.cat([doc_start.view(B, T), tail], dim=1).contiguous().view(-1)
+        return ids, B, T, T_run, doc_start
+
     def _trunk(self, ids: torch.Tensor, rt: _Runtime):
         self._attach_grads()
         L = self.layout
@@ -395,8 +419,8 @@ class Transformer(nn.Module):
                 deterministic: bool = True) -> torch.Tensor:
         """Transformer.__call__ (transformer.py:346-407) -> logits [B, T, V] bf16.  `attn_mask`, if given, must be the
         bool [B,T,T] block-diagonal causal mask train_lm.py builds; it is converted to document starts."""
-        ids, B, T, doc_start = self._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
-        rt = self._runtime(B, T, doc_start)
+        ids, B, T, T_run, doc_start = self._prep_padded(input_ids, attn_mask, doc_lengths, doc_start)
+        rt = self._runtime(B, T_run, doc_start)
         res, delta = self._trunk(ids, rt)
         res_f, hf = ops.RMSNormResidualFn.apply(res, delta, self.head.out_norm, self.head.g_out_norm, rt.eps)
         if self.head.tied:
@@ -406,7 +430,7 @@ class Transformer(nn.Module):
             logits = ops.head_logits(hf, self.head)
         else:
             logits = ops.LinearFn.apply(hf, self.head.w_lm, self.head.g_lm)
-        return logits.view(B, T, self.layout.V_pad)[:, :, : self.cfg.vocab_size]
+        return logits.view(B, T_run, self.layout.V_pad)[:, :T, : self.cfg.vocab_size]
 
     def loss_and_acc(self, input_ids: torch.Tensor, labels: torch.Tensor, *,
                      doc_lengths: Optional[Sequence[Sequence[int]]] = None, doc_start: Optional[torch.Tensor] = None,
@@ -414,13 +438,17 @@ class Transformer(nn.Module):
         """model.apply + _loss_and_acc (train_lm.py:259-265, :181-186) -> (loss, acc) 0-dim fp32 tensors.
         `loss_scale` pre-scales the gradients (1/grad_accumulation_steps); `unit_grad=True` promises that
         loss.backward() is called with the default unit gradient (saves a device->host read of it)."""
-        ids, B, T, doc_start = self._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
+        ids, B, T, T_run, doc_start = self._prep_padded(input_ids, attn_mask, doc_lengths, doc_start)
         if tuple(labels.shape) != (B, T):
             raise ValueError("labels must match input_ids' shape")
-        lab = labels.to(device=ids.device, dtype=torch.int32, non_blocking=True).contiguous().view(-1)
-        rt = self._runtime(B, T, doc_start)
+        lab = labels.to(device=ids.device, dtype=torch.int32, non_blocking=True).contiguous()
+        pad = None
+        if T_run != T:
+            lab = torch.nn.functional.pad(lab, (0, T_run - T)).contiguous()
+            pad = (B, T, T_run)
+        rt = self._runtime(B, T_run, doc_start)
         res, delta = self._trunk(ids, rt)
-        out2 = ops.HeadLossFn.apply(res, delta, lab, self.head, rt, loss_scale, unit_grad)
+        out2 = ops.HeadLossFn.apply(res, delta, lab.view(-1), self.head, rt, loss_scale, unit_grad, pad)
         return out2[0], out2[1]
 
 

@@ -241,7 +241,25 @@ def head_logits_ce(hf: torch.Tensor, head) -> Tuple[torch.Tensor, torch.Tensor]:
     return logits, ce_ms
 
 
-def ce_from_stats(logits: torch.Tensor, labels: torch.Tensor, ce_ms: torch.Tensor, V: int, grad_scale: float):
+def _ce_means(lib, row_loss: torch.Tensor, row_correct: torch.Tensor, dlogits: Optional[torch.Tensor], pad) -> torch.Tensor:
+    """[mean loss, mean acc] over the rows that count.  pad = None: all M rows (pcv_mean2).  pad = (B, T, T_run): the
+    sequences were padded from T to T_run positions (T not a multiple of the attention tile, model.Transformer
+    ._prep_padded); the pad rows are left out of both means and their d(logits) rows are zeroed, so that nothing flows
+    back from them (a pad query does see real keys)."""
+    M = row_loss.shape[0]
+    if pad is None:
+        out2 = torch.empty((2,), dtype=torch.float32, device=row_loss.device)
+        check(lib.pcv_mean2(row_loss.data_ptr(), row_correct.data_ptr(), out2.data_ptr(), M, _stream()), "pcv_mean2")
+        return out2
+    B, T, T_run = pad
+    inv = 1.0 / float(B * T)
+    out2 = torch.stack([row_loss.view(B, T_run)[:, :T].sum(), row_correct.view(B, T_run)[:, :T].sum()]) * inv
+    if dlogits is not None:
+        dlogits.view(B, T_run, dlogits.shape[1])[:, T:, :].zero_()
+    return out2
+
+
+def ce_from_stats(logits: torch.Tensor, labels: torch.Tensor, ce_ms: torch.Tensor, V: int, grad_scale: float, pad=None):
     """-> (out2 = [mean loss, mean acc], dlogits): second half of the fused head + cross-entropy (pcv_ce_from_stats);
     dlogits overwrites `logits`."""
     M, ldl = logits.shape
@@ -251,9 +269,7 @@ def ce_from_stats(logits: torch.Tensor, labels: torch.Tensor, ce_ms: torch.Tenso
     check(lib.pcv_ce_from_stats(logits.data_ptr(), labels.data_ptr(), ce_ms.data_ptr(), ce_ms.shape[0], logits.data_ptr(),
                                 row_loss.data_ptr(), row_correct.data_ptr(), M, V, ldl, grad_scale, _stream()),
           "pcv_ce_from_stats")
-    out2 = torch.empty((2,), dtype=torch.float32, device=logits.device)
-    check(lib.pcv_mean2(row_loss.data_ptr(), row_correct.data_ptr(), out2.data_ptr(), M, _stream()), "pcv_mean2")
-    return out2, logits
+    return _ce_means(lib, row_loss, row_correct, logits, pad), logits
 
 
 def head_dgrad(dlogits: torch.Tensor, head, alpha: float) -> torch.Tensor:
@@ -300,7 +316,7 @@ def attn_bwd(qkv: torch.Tensor, cos_sin: torch.Tensor, doc_start: Optional[torch
     return dqkv
 
 
-def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, V: int, grad_scale: float, write_grad: bool):
+def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, V: int, grad_scale: float, write_grad: bool, pad=None):
     """-> (out2 = [mean loss, mean acc] fp32 device tensor, dlogits or None).  dlogits overwrites `logits`."""
     M, ldl = logits.shape
     row_loss = torch.empty((M,), dtype=torch.float32, device=logits.device)
@@ -309,9 +325,7 @@ def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, V: int, grad_scale: f
     check(lib.pcv_softmax_ce(logits.data_ptr(), labels.data_ptr(), logits.data_ptr() if write_grad else None,
                              row_loss.data_ptr(), row_correct.data_ptr(), M, V, ldl, grad_scale, _stream()),
           "pcv_softmax_ce")
-    out2 = torch.empty((2,), dtype=torch.float32, device=logits.device)
-    check(lib.pcv_mean2(row_loss.data_ptr(), row_correct.data_ptr(), out2.data_ptr(), M, _stream()), "pcv_mean2")
-    return out2, (logits if write_grad else None)
+    return _ce_means(lib, row_loss, row_correct, logits if write_grad else None, pad), (logits if write_grad else None)
 
 
 # ------------------------------------------------------------------------------------------------ tangents (N4)
@@ -597,18 +611,19 @@ class HeadLossFn(torch.autograd.Function):
     fp32 [M,V] logits of the reference are never materialised."""
 
     @staticmethod
-    def forward(ctx, res, delta, labels, head, rt, loss_scale, unit_grad):
+    def forward(ctx, res, delta, labels, head, rt, loss_scale, unit_grad, pad=None):
         res_f, hf, rstd = rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
         M = hf.shape[0]
+        n_tok = M if pad is None else pad[0] * pad[1]  # the mean of _loss_and_acc runs over the real tokens
         need_grad = bool(ctx.needs_input_grad[0])
         if need_grad and _HEAD_CE_FUSED:
             # the head GEMM's epilogue leaves the per-slot softmax partials, one streaming pass turns the logits into
             # d(logits) (one exponential per logit): loss kernels 0.78 -> 0.63 ms, head GEMM +0.06 ms at C3 (DESIGN §4)
             logits, ce_ms = head_logits_ce(hf, head)
-            out2, dlogits = ce_from_stats(logits, labels, ce_ms, head.vocab, loss_scale / M)
+            out2, dlogits = ce_from_stats(logits, labels, ce_ms, head.vocab, loss_scale / n_tok, pad)
         else:
             logits = head_logits(hf, head)
-            out2, dlogits = softmax_ce(logits, labels, head.vocab, loss_scale / M, need_grad)
+            out2, dlogits = softmax_ce(logits, labels, head.vocab, loss_scale / n_tok, need_grad, pad)
         if need_grad:
             ctx.save_for_backward(res_f, rstd, hf, dlogits)
         ctx.head, ctx.has_delta, ctx.unit_grad = head, delta is not None, unit_grad
@@ -628,4 +643,4 @@ class HeadLossFn(torch.autograd.Function):
         wgrad_stream.join(d_r.device)
         if head.on_grads_ready is not None:
             head.on_grads_ready()
-        return d_r, (d_r if ctx.has_delta else None), None, None, None, None, None
+        return d_r, (d_r if ctx.has_delta else None), None, None, None, None, None, None

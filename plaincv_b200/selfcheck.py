@@ -31,7 +31,7 @@ def reducer_exact_check(model, rank: int, world: int, process_group=None,
     """The CUDA branch of GradReducer in isolation, on known numbers (no run-to-run noise): every rank fills the flat
     gradient buffer with its own seeded values, fires every bucket (communication stream, event fences, bf16 cast round
     trip, NCCL AVG) and compares with the mean it computes locally from all ranks' seeds.  fp32 wire must agree to fp32
-    summation order; bf16 wire to two bf16 roundings (<= 4e-3 rel. L2)."""
+    summation order; bf16 wire to its roundings (<= 2e-3 x sqrt(world + 1) rel. L2, see ddp_gradient_check)."""
     dev = model.flat_grad.device
     n = model.flat_grad.numel()
 
@@ -139,6 +139,10 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
     ex_bf16, ex_fp32, ex_uncovered = (float(x) for x in ex)
     # whole-step comparisons cannot be tighter than two runs of the SAME single-rank step are to each other
     step_tol = max(4e-3, 2.0 * noise)
+    # bf16 on the wire: every rank's bucket is rounded once (2^-9 / sqrt(3) rms), the all-reduce adds in bf16 (one more
+    # rounding per addition, world - 1 of them along a ring or tree) and the mean is rounded on the way back: the rms
+    # error grows like sqrt(world + 1).  Measured: 2.45e-3 on 2 GPUs, 4.04e-3 on 8 = 1.4e-3 x sqrt(world + 1).
+    wire_tol = 2e-3 * (world + 1) ** 0.5
     out.update({
         "world": world, "micro_batches_per_rank": 1,
         "rel_l2_bf16_wire": v[0], "rel_l2_fp32_wire": v[1],
@@ -149,10 +153,12 @@ def ddp_gradient_check(model, seq_len: int, use_doc_mask: bool, global_batches: 
         "ranks_hold_identical_gradients": bool(float(cmin) == float(cmax)),
         "reducer_exact_rel_l2_bf16_wire": ex_bf16, "reducer_exact_rel_l2_fp32_wire": ex_fp32,
         "overlap_off_equal": bool(v[2] <= step_tol and v[3] <= step_tol),
-        "ok": bool(ex_bf16 <= 4e-3 and ex_fp32 <= 1e-6 and ex_uncovered == 0.0 and v[0] <= step_tol and v[1] <= step_tol
+        "reducer_bf16_wire_tolerance": wire_tol,
+        "ok": bool(ex_bf16 <= wire_tol and ex_fp32 <= 1e-6 and ex_uncovered == 0.0 and v[0] <= step_tol and v[1] <= step_tol
                    and v[2] <= step_tol and v[3] <= step_tol and v[7] <= step_tol and v[5] <= 1e-4
                    and float(cmin) == float(cmax)),
-        "tolerance": "reducer alone on known numbers (no noise): bf16 wire <= 4e-3, fp32 wire <= 1e-6 of the exact mean; "
+        "tolerance": "reducer alone on known numbers (no noise): bf16 wire <= 2e-3 x sqrt(world + 1) (one rounding per rank's "
+                     "bucket, per bf16 addition inside the all-reduce and of the mean), fp32 wire <= 1e-6 of the exact mean; "
                      "whole step (bf16 / fp32 wire, overlap off, CUDA-graph replay, each against the single-rank gradient "
                      "of the whole global batch or its eager twin) <= max(4e-3, 2 x rel_l2_rerun_noise), the noise being the "
                      "largest pairwise distance of three runs of the same single-rank step: such runs differ by the order of fp32 reduce-adds (split-K wgrad, dQ), which "

@@ -113,6 +113,31 @@ def test_logits_api_matches_oracle():
         assert rel_l2(grads[k], g_ref[k]) < 1.5e-2, k
 
 
+@pytest.mark.parametrize("seq_len,use_doc", [(200, False), (200, True), (72, False), (328, True)])
+def test_ragged_sequence_length_parity(seq_len, use_doc):
+    """Sequence lengths that are not multiples of the attention tile (the reference takes any T <= seq_len and slices
+    freqs_cis to it, transformer.py:373-374): sequences run right-padded to the next multiple of 128, the pad rows stay
+    out of the loss / accuracy means and send nothing back.  Loss and every parameter gradient against the fp32 oracle on
+    the un-padded batch, at the whole-path tolerances."""
+    cfg_o = O.ModelConfig(vocab_size=1003, seq_len=seq_len, dim=128, expand=8 / 3, n_layers=2, n_heads=2)
+    model, params = _build(cfg_o, seed=5)
+    batch = O.synthetic_batch(3, seq_len, 1003, seed=21, doc_mean=50 if use_doc else None)
+    _compare(model, params, cfg_o, batch, use_doc)
+    # the logits API drops the pad rows; a batch shorter than cfg.seq_len is accepted as in the reference
+    inputs, labels, mask = O.prepare_batch(batch, seq_len, use_doc)
+    T_short = seq_len - 17
+    with torch.no_grad():
+        logits = model(inputs[:, :T_short], None if mask is None else mask[:, :T_short, :T_short])
+    assert tuple(logits.shape) == (3, T_short, 1003)
+    ref = O.forward(params, cfg_o, inputs[:, :T_short], None if mask is None else mask[:, :T_short, :T_short], torch.float32)
+    assert rel_l2(logits, ref) < 1e-2
+    # accuracy counts real tokens only: against the oracle's own bf16-free value
+    from plaincv_b200.engine import Engine
+    _, acc = Engine(model, seq_len=seq_len, use_doc_mask=use_doc).eval_step(batch)
+    _, _, acc_ref = O.compute_grads(params, cfg_o, inputs, labels, mask, torch.float32)
+    assert abs(float(acc) - float(acc_ref)) <= 2.0 / (3 * seq_len)
+
+
 def test_grad_accumulation_and_linearity():
     """train_step over two micro-batches == mean of the two single-batch gradients (size-independent property)."""
     from plaincv_b200.engine import Engine
