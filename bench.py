@@ -107,7 +107,35 @@ class ClockSampler:
         self._stop = threading.Event()
         self._t = None
 
+    def _run_nvml(self) -> bool:
+        """Preferred: NVML in-process (a sample costs well under a millisecond; eight ranks forking nvidia-smi at once
+        got two samples into a one-second timed region).  False if NVML cannot be used: the caller forks nvidia-smi."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            smax = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            bits = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                    ("sw_power_cap", 0x4))
+            float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))  # (raises here rather than inside the loop)
+        except Exception:
+            return False
+        while not self._stop.is_set():
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                mask = int(get_reasons(h))
+                watts = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                self.rows.append([str(sm), str(smax), str(watts)] + [("Active" if mask & b else "Not Active") for _, b in bits])
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+        return True
+
     def _run(self):
+        if self._run_nvml():
+            return
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
