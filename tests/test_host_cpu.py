@@ -135,6 +135,28 @@ def test_bucket_groups_partition_the_layers_in_backward_order():
             assert groups[-1] == (0, 0)
 
 
+def test_padded_rows_stay_out_of_the_loss_means():
+    """Host side of ragged sequence lengths (model.Transformer._prep_padded / ops._ce_means): with sequences padded from
+    T to T_run positions, loss and accuracy are means over the B*T real tokens (_loss_and_acc, train_lm.py:181-186) and
+    the pad rows of d(logits) are zeroed; real rows are untouched."""
+    from plaincv_b200 import ops
+    B, T, T_run, V = 3, 5, 8, 16
+    g = torch.Generator().manual_seed(0)
+    row_loss = torch.rand(B * T_run, generator=g)
+    row_correct = (torch.rand(B * T_run, generator=g) > 0.5).float()
+    dlogits = torch.randn(B * T_run, V, generator=g)
+    keep = dlogits.clone()
+    out2 = ops._ce_means(None, row_loss, row_correct, dlogits, (B, T, T_run))
+    real = torch.zeros(B, T_run, dtype=torch.bool)
+    real[:, :T] = True
+    real = real.view(-1)
+    assert torch.allclose(out2[0], row_loss[real].mean()) and torch.allclose(out2[1], row_correct[real].mean())
+    assert torch.equal(dlogits[real], keep[real]) and float(dlogits[~real].abs().sum()) == 0.0
+    # evaluation (no gradient tensor) takes the same means
+    out2e = ops._ce_means(None, row_loss, row_correct, None, (B, T, T_run))
+    assert torch.equal(out2e, out2)
+
+
 def test_product_path_refuses_cpu():
     from plaincv_b200.model import ModelConfig, Transformer
     cfg = ModelConfig(vocab_size=64, seq_len=64, dim=64, expand=8 / 3, n_layers=1, n_heads=1)
