@@ -138,6 +138,33 @@ def test_ragged_sequence_length_parity(seq_len, use_doc):
     assert abs(float(acc) - float(acc_ref)) <= 2.0 / (3 * seq_len)
 
 
+@pytest.mark.parametrize("case", ["one_sequence_one_tile", "one_token_documents", "extreme_and_repeated_tokens"])
+def test_edge_case_batches_parity(case):
+    """Edges of the batch contract (train_lm.py:97-148): a single sequence of a single attention tile; documents of one
+    token (every position attends only itself: the mask's extreme) mixed with longer ones; token ids at both ends of a
+    vocabulary that is not a multiple of 8, with long runs of one repeated token (the embedding gradient's scatter-add
+    collides on one row, labels pick the last real logit column).  Loss and every gradient against the fp32 oracle."""
+    V = 50257 if case == "extreme_and_repeated_tokens" else 1003
+    T = 128 if case == "one_sequence_one_tile" else 256
+    B = 1 if case == "one_sequence_one_tile" else 2
+    cfg_o = O.ModelConfig(vocab_size=V, seq_len=T, dim=128, expand=8 / 3, n_layers=1 if B == 1 else 2, n_heads=2)
+    model, params = _build(cfg_o, seed=6)
+    batch = O.synthetic_batch(B, T, V, seed=31)
+    use_doc = False
+    if case == "one_token_documents":
+        use_doc = True
+        # row 0: T + 1 documents of one token; row 1: one-token documents around two longer ones
+        batch["docs_lengths"] = [[1] * (T + 1), [1] * 7 + [100] + [1] * 50 + [T + 1 - 7 - 100 - 50]]
+    if case == "extreme_and_repeated_tokens":
+        ids = np.array(batch["input_ids"])
+        ids[0, :100] = V - 1
+        ids[0, 100:180] = 0
+        ids[1, ::2] = V - 1
+        ids[1, 1::2] = 0
+        batch["input_ids"] = ids
+    _compare(model, params, cfg_o, batch, use_doc)
+
+
 def test_grad_accumulation_and_linearity():
     """train_step over two micro-batches == mean of the two single-batch gradients (size-independent property)."""
     from plaincv_b200.engine import Engine
