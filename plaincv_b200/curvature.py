@@ -145,14 +145,19 @@ def jvp_logits(model: Transformer, input_ids: torch.Tensor, tangent: TangentBuff
                attn_mask: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """jax.jvp(logits_fn, (params,), (vec,)) of optim/ggn_utils.py:110-114 -> (logits, J vec), both bf16
     [B*T, V_pad] (pad columns zero)."""
-    ids, B, T, doc_start = model._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
-    rt = model._runtime(B, T, doc_start)
+    ids, B, T, T_run, doc_start = model._prep_padded(input_ids, attn_mask, doc_lengths, doc_start)
+    rt = model._runtime(B, T_run, doc_start)
     rt.tape = []
     res, delta = model._trunk(ids, rt)
     head = model.head
     res_f, hf, rstd = ops.rmsnorm_residual_fwd(res, delta, head.out_norm, rt.eps)
     logits = _head_matmul(hf, head.w_lm, head)
-    return logits, _tangent_pass(model, ids, rt, rt.tape, (res_f, rstd, hf), tangent)
+    tlogits = _tangent_pass(model, ids, rt, rt.tape, (res_f, rstd, hf), tangent)
+    if T_run != T:  # a ragged T ran right-padded (Transformer._prep_padded): drop the pad rows
+        Vp = logits.shape[1]
+        logits = logits.view(B, T_run, Vp)[:, :T].reshape(B * T, Vp)
+        tlogits = tlogits.view(B, T_run, Vp)[:, :T].reshape(B * T, Vp)
+    return logits, tlogits
 
 
 def ggn_product_accumulate(model: Transformer, input_ids: torch.Tensor, tangent: TangentBuffers, out_scale: float, *,
@@ -161,8 +166,8 @@ def ggn_product_accumulate(model: Transformer, input_ids: torch.Tensor, tangent:
     """model.flat_grad += out_scale * J^T H J vec for one batch (optim/ggn_utils.py:94-131): ONE primal forward feeds
     both the tangent pass (jax.jvp, :110-114) and the transpose (jax.vjp, :129-131) — the blocks leave their saved
     activations on a tape; the Hessian-vector product (:116-127) overwrites J vec in place."""
-    ids, B, T, doc_start = model._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
-    rt = model._runtime(B, T, doc_start)
+    ids, B, T, T_run, doc_start = model._prep_padded(input_ids, attn_mask, doc_lengths, doc_start)
+    rt = model._runtime(B, T_run, doc_start)
     rt.tape = []
     box: dict = {}
     with torch.enable_grad():
@@ -174,6 +179,8 @@ def ggn_product_accumulate(model: Transformer, input_ids: torch.Tensor, tangent:
         rt.tape = None
         logits = _head_matmul(head_state[2], model.head.w_lm, model.head)
         box["cot"] = ops.ce_hessian_vec(logits, tlogits, model.cfg.vocab_size, out_scale, out=tlogits)
+        if T_run != T:  # pad rows of a ragged T carry no loss: their cotangent is zero (a pad query does see real keys)
+            box["cot"].view(B, T_run, -1)[:, T:, :].zero_()
         del logits, tlogits, head_state
     dummy.backward()
 
@@ -183,10 +190,12 @@ def vjp_logits_accumulate(model: Transformer, input_ids: torch.Tensor, cotangent
                           attn_mask: Optional[torch.Tensor] = None) -> None:
     """jax.vjp(logits_fn, params)[1](cotangent) of optim/ggn_utils.py:129-130, ADDED into model.flat_grad
     (param.grad are views of it).  cotangent: bf16 [B*T, V_pad]."""
-    ids, B, T, doc_start = model._prep_inputs(input_ids, attn_mask, doc_lengths, doc_start)
+    ids, B, T, T_run, doc_start = model._prep_padded(input_ids, attn_mask, doc_lengths, doc_start)
     if tuple(cotangent.shape) != (B * T, model.layout.V_pad) or cotangent.dtype != torch.bfloat16:
         raise ValueError("cotangent must be bf16 [B*T, V_pad]")
-    rt = model._runtime(B, T, doc_start)
+    if T_run != T:
+        cotangent = torch.nn.functional.pad(cotangent.view(B, T, -1), (0, 0, 0, T_run - T)).reshape(B * T_run, -1)
+    rt = model._runtime(B, T_run, doc_start)
     with torch.enable_grad():
         res, delta = model._trunk(ids, rt)
         box = {"cot": cotangent.contiguous()}

@@ -177,11 +177,12 @@ def _dot(a, b):
     return sum(float((a[k].double().cpu() * b[k].double().cpu()).sum()) for k in a)
 
 
-@pytest.mark.parametrize("mlp,tied,use_doc", [("glu", False, False), ("glu", False, True), ("mlp", True, False),
-                                              ("mlp_relu_sq", False, False)])
-def test_jvp_and_ggn_matvec_against_oracle(mlp, tied, use_doc):
+@pytest.mark.parametrize("mlp,tied,use_doc,T", [("glu", False, False, 256), ("glu", False, True, 256), ("mlp", True, False, 256),
+                                                ("mlp_relu_sq", False, False, 256), ("glu", False, True, 200)])
+def test_jvp_and_ggn_matvec_against_oracle(mlp, tied, use_doc, T):
+    """(the T = 200 case: a sequence length that is not a multiple of the attention tile runs right-padded)"""
     from plaincv_b200.curvature import TangentBuffers, jvp_logits, make_ggn_matvec_fn_lm
-    V, T, B = 1000, 256, 2
+    V, B = 1000, 2
     cfg_o = O.ModelConfig(vocab_size=V, seq_len=T, dim=128, expand=8 / 3, n_layers=2, n_heads=2, mlp=mlp,
                           tie_embeddings=tied)
     model, params = _build(cfg_o, seed=5)
