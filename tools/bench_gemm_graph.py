@@ -41,6 +41,10 @@ rows = []
 shapes = (("qkv", d, 3 * d), ("out", d, d), ("gu", d, 2 * hp), ("down", hp, d))
 if os.environ.get("PCV_GG_LM", "0") == "1":
     shapes = shapes + (("lm", d, Vp),)
+if os.environ.get("PCV_GG_ONLY"):
+    shapes = tuple(sh for sh in (shapes + (("lm", d, Vp),)) if sh[0] in os.environ["PCV_GG_ONLY"].split(","))
+    shapes = tuple(dict.fromkeys(shapes))
+NOCUBLAS = os.environ.get("PCV_GG_NOCUBLAS", "0") == "1"
 for name, K, N in shapes:
     sets = SETS if name != "lm" else 1
     x = [torch.randn(M, K, device=dev).to(bf) for _ in range(sets)]
@@ -60,7 +64,7 @@ for name, K, N in shapes:
          lambda i: torch.matmul(x[i % sets].t(), dy[i % sets], out=dwb[i % sets])),
     ):
         t_o = graph_time(ours)
-        t_l = graph_time(lib)
+        t_l = t_o if NOCUBLAS else graph_time(lib)
         rows.append((f"{op}_{name}", t_o, t_l))
         print(f"{op+'_'+name:14s} ours {t_o:8.1f} us {fl/t_o/1e6:8.1f} TFLOP/s | cublas {t_l:8.1f} us {fl/t_l/1e6:8.1f} TFLOP/s | ours/cublas time {t_o/t_l:5.3f}", flush=True)
     del x, w, dy, y, dx, dwb, dwf
